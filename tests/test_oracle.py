@@ -1,0 +1,234 @@
+"""CPU tests of the oracle (oracle/dietgpu_oracle.c) against the reference's known answers.
+
+The reference holds no golden byte streams; what it does pin is restated
+here: table normalisation (dietgpu/ans/ANSStatisticsTest.cu:127-207), sizes %16
+(dietgpu/ans/ANSTest.cu:131-135), round trips at the reference's own test sizes
+(ANSTest.cu:243-282, float/FloatTest.cu:287-341), max-size formulas, and the committed
+fixtures under tests/golden/ that freeze the oracle's byte streams once validated against the
+reference's CUDA build on the GPU box.
+"""
+import numpy as np
+import pytest
+
+import oracle as O
+from datagen import BFLOAT16, FLOAT16, FLOAT32, FLOAT64, exp_bytes, float_words
+
+ALL_FT = [FLOAT16, BFLOAT16, FLOAT32, FLOAT64]
+
+
+# ---- sizes ------------------------------------------------------------------------
+def test_max_sizes():
+    # 1 MiB -> 1 868 320 B
+    assert O.ans_max_compressed_size(1 << 20) == 1868320
+    assert O.ans_max_compressed_size(0) == 557600
+    n = 12345
+    assert O.float_raw_section_bytes(FLOAT16, n) == 12352
+    assert O.float_raw_section_bytes(FLOAT32, n) == 2 * 12352 + 12352
+    assert O.float_raw_section_bytes(FLOAT64, n) == 4 * 12348 + 2 * 12352
+    assert O.float_max_compressed_size(BFLOAT16, n) == 32 + O.ans_max_compressed_size(n) + 12352
+    assert O.float_max_compressed_size(FLOAT64, n) == (
+        32 + 2 * O.ans_max_compressed_size(n) + O.float_raw_section_bytes(FLOAT64, n))
+    assert O.sparse_float_max_compressed_size(FLOAT32, n) == (
+        16 + 1552 + O.float_max_compressed_size(FLOAT32, n))
+
+
+# ---- normalisation known answers (ANSStatisticsTest.cu) -----------------------------
+def test_normalization_nonzero():
+    data = np.ones(10000, np.uint8)
+    data[:256] = np.arange(256, dtype=np.uint8)
+    pdf, cdf = O.normalize(O.histogram(data), data.size, 10)
+    expect = np.ones(256, np.uint32)
+    expect[1] = 1024 - 255
+    assert (pdf == expect).all()
+    assert (cdf == np.concatenate([[0], np.cumsum(expect)[:-1]])).all()
+
+
+def test_normalization_equal_weight():
+    data = np.tile(np.arange(256, dtype=np.uint8), 64)
+    pdf, _ = O.normalize(O.histogram(data), data.size, 10)
+    assert (pdf == 4).all()
+
+
+@pytest.mark.parametrize("pb", [9, 10, 11])
+def test_normalization_invariants(pb):
+    data = exp_bytes(12345, lam=40.0)
+    hist = O.histogram(data)
+    pdf, _ = O.normalize(hist, data.size, pb)
+    total = 1 << pb
+    assert int(pdf.sum()) == total
+    for s in range(256):
+        if hist[s] == 0:
+            assert pdf[s] == 0
+        else:
+            assert pdf[s] > 0
+            if pb != 11:  # the reference pins the 2x bounds at probBits 11 only (:175)
+                continue
+            prob = np.float32(hist[s]) / np.float32(data.size)
+            norm = np.float32(pdf[s]) / np.float32(total)
+            assert norm >= prob * np.float32(0.5)
+            if prob > np.float32(1.0) / np.float32(total):
+                assert norm <= prob * np.float32(2.0)
+
+
+def test_normalization_symbol_id_quirk():
+    # diff > 0 adds 1 to every entry whose SYMBOL ID < diff — even a symbol that is absent
+    # (dietgpu/ans/GpuANSStatistics.cuh:258-273).  counts: sym 200 x3, sym 201 x3, sym 202 x1:
+    # q = trunc(1024 * c / 7) = 438, 438, 146 -> sum 1022, diff 2 -> symbols 0 and 1 get +1.
+    hist = np.zeros(256, np.uint32)
+    hist[200], hist[201], hist[202] = 3, 3, 1
+    pdf, _ = O.normalize(hist, 7, 10)
+    assert pdf[0] == 1 and pdf[1] == 1
+    assert pdf[200] == 438 and pdf[201] == 438 and pdf[202] == 146
+    assert int(pdf.sum()) == 1024
+
+
+def test_histogram_and_checksum():
+    for n in [1, 7, 15, 16, 17, 4095, 4096, 4097, 123457]:
+        d = exp_bytes(n, seed=n)
+        assert (O.histogram(d) == np.bincount(d, minlength=256)).all()
+        assert O.checksum(d) == int(np.bitwise_xor.reduce(d))
+
+
+# ---- ANS round trips at the reference's test sizes (ANSTest.cu:243-282) --------------
+ANS_SIZES = [0, 1, 31, 32, 33, 4095, 4096, 4097, 1234, 2345, 3456, 10000, 10013, 8192 + 16]
+
+
+@pytest.mark.parametrize("pb", [9, 10, 11])
+@pytest.mark.parametrize("lam", [1.0, 10.0, 100.0, 1000.0])
+def test_ans_round_trip(pb, lam):
+    for n in ANS_SIZES:
+        d = exp_bytes(n, lam=lam, seed=10 + n)
+        a = O.ans_encode(d, pb, use_checksum=True)
+        assert a.size % 16 == 0
+        hdr = a[:32].view(np.uint32)
+        nb = (n + 4095) // 4096
+        assert hdr[0] == 0xD00D0001 and hdr[1] == nb and hdr[2] == n
+        assert hdr[4] == (pb | 0x10) and hdr[5] == O.checksum(d)
+        assert a.size == 32 + 512 + 128 * nb + 8 * ((nb + 1) // 2 * 2) + 2 * hdr[3]
+        ok, sz, out = O.ans_decode(a)
+        assert ok and sz == n and (out == d).all()
+        ok, sz, _ = O.ans_decode(a, capacity=max(n - 1, 0))
+        assert sz == n and ok == (n == 0)
+
+
+def test_ans_random_sizes():
+    rng = np.random.default_rng(3)
+    for n in rng.integers(100, 10001, size=30):
+        d = exp_bytes(int(n), lam=20.0, seed=int(n))
+        ok, sz, out = O.ans_decode(O.ans_encode(d))
+        assert ok and sz == n and (out == d).all()
+
+
+def test_ans_incompressible_block_bound():
+    # uniform random bytes at probBits 10: every block stays within the reference's 5120 B
+    # staging bound (dietgpu/ans/GpuANSEncode.cuh:31-36)
+    rng = np.random.default_rng(5)
+    d = rng.integers(0, 256, size=1 << 16, dtype=np.uint8)
+    a = O.ans_encode(d, 10)
+    nb = 16
+    bw = a[544 + 128 * nb:544 + 128 * nb + 8 * nb].view(np.uint32)[0::2] & 0xFFFF
+    assert (bw * 2 <= 5120).all()
+    ok, _, out = O.ans_decode(a)
+    assert ok and (out == d).all()
+
+
+def test_ans_defined_mask_covers_all_nonzero_bytes():
+    d = exp_bytes(10013, seed=7)
+    for cs in (False, True):
+        a = O.ans_encode(d, 10, use_checksum=cs)
+        m = O.ans_defined_mask(a)
+        assert m.size == a.size
+        assert (a[~m] == 0).all()  # the oracle writes 0 wherever the reference is undefined
+
+
+def test_ans_supplied_histogram_matches():
+    d = exp_bytes(50000, seed=9)
+    assert (O.ans_encode(d, 10, hist=O.histogram(d)) == O.ans_encode(d, 10)).all()
+
+
+# ---- float round trips (FloatTest.cu:287-341) ----------------------------------------
+FLOAT_SIZES = [0, 1, 2, 13, 17, 4096, 8083, 12345, 10000, 65536 + 5]
+
+
+@pytest.mark.parametrize("ft", ALL_FT)
+@pytest.mark.parametrize("pb", [9, 10])
+def test_float_round_trip(ft, pb):
+    for n in FLOAT_SIZES:
+        w = float_words(ft, n, seed=10 + n)
+        a = O.float_compress(ft, w, pb, use_checksum=True)
+        assert a.size % 16 == 0
+        hdr = a[:32].view(np.uint32)
+        assert hdr[0] == 0xF00F0001 and hdr[1] == n and hdr[2] == (ft | 0x10)
+        R = O.float_raw_section_bytes(ft, n)
+        ans0 = a[32 + R:]
+        assert ans0[:4].view(np.uint32)[0] == 0xD00D0001
+        assert hdr[4] == 544 + 128 * ans0[4:8].view(np.uint32)[0] + 8 * (
+            (ans0[4:8].view(np.uint32)[0] + 1) // 2 * 2) + 2 * ans0[12:16].view(np.uint32)[0]
+        ok, sz, out = O.float_decompress(a)
+        assert ok and sz == n and (out == w).all()
+        m = O.float_defined_mask(a)
+        assert m.size == a.size and (a[~m] == 0).all()
+
+
+def test_float_ratio_bf16_fp16():
+    # README.md:118: bf16 ~0.67x, fp16 ~0.85x on N(0,1)
+    n = 1 << 18
+    r_bf16 = O.float_compress(BFLOAT16, float_words(BFLOAT16, n)).size / (2 * n)
+    r_f16 = O.float_compress(FLOAT16, float_words(FLOAT16, n)).size / (2 * n)
+    assert 0.62 < r_bf16 < 0.72
+    assert 0.80 < r_f16 < 0.90
+
+
+def test_float_special_values():
+    w = np.array([0, 0x80000000, 0x7F800000, 0xFF800000, 0x7FC00000, 1, 0xFFFFFFFF, 0x3F800000],
+                 np.uint32)
+    ok, _, out = O.float_decompress(O.float_compress(FLOAT32, w))
+    assert ok and (out == w).all()
+    w64 = np.array([0, 1 << 63, 0x7FF0000000000000, 0xFFFFFFFFFFFFFFFF, 0x3FF0000000000000],
+                   np.uint64)
+    ok, _, out = O.float_decompress(O.float_compress(FLOAT64, w64))
+    assert ok and (out == w64).all()
+
+
+# ---- sparse (SparseFloatBenchmark.cu:126-140, :359-373) -------------------------------
+@pytest.mark.parametrize("ft", ALL_FT)
+@pytest.mark.parametrize("sparsity", [0.0, 0.5, 0.9, 1.0])
+def test_sparse_round_trip(ft, sparsity):
+    for n in [0, 1, 2, 7, 8, 9, 127, 128, 129, 100000]:
+        w = float_words(ft, n, seed=n + 1, sparsity=sparsity)
+        a = O.sparse_float_compress(ft, w)
+        assert a.size % 16 == 0 and a[:4].view(np.uint32)[0] == n
+        ok, sz, out = O.sparse_float_decompress(ft, a)
+        assert ok and sz == n and (out == w).all()
+        m = O.sparse_float_defined_mask(ft, a)
+        assert m.size == a.size and (a[~m] == 0).all()
+
+
+def test_sparse_bitmap_msb_first_and_negative_zero():
+    w = np.zeros(16, np.uint32)
+    w[0] = 0x3F800000
+    w[9] = 0x80000000  # -0.0 is "non-zero" (integer compare)
+    a = O.sparse_float_compress(FLOAT32, w)
+    assert a[16] == 0x80 and a[17] == 0x40
+    assert a[16 + 16 + 4:16 + 16 + 8].view(np.uint32)[0] == 2  # embedded float archive: nnz
+
+
+# ---- batched drivers agree with the single-archive entry points ------------------------
+def test_batch_drivers():
+    ins = [exp_bytes(n, seed=n) for n in [4096, 10013, 1, 70000]]
+    outs = [np.zeros(O.ans_max_compressed_size(a.size), np.uint8) for a in ins]
+    ob = O.ans_encode_batch(ins, outs)
+    for a, o, b in zip(ins, outs, ob):
+        assert (o[:b] == O.ans_encode(a)).all()
+    dec = [np.zeros(a.size, np.uint8) for a in ins]
+    sz = O.ans_decode_batch(outs, dec)
+    assert all((d == a).all() for d, a in zip(dec, ins)) and list(sz) == [a.size for a in ins]
+
+    fins = [float_words(FLOAT32, n, seed=n) for n in [5000, 1, 33333]]
+    fouts = [np.zeros(O.float_max_compressed_size(FLOAT32, a.size), np.uint8) for a in fins]
+    ob = O.float_compress_batch(FLOAT32, fins, fouts)
+    for a, o, b in zip(fins, fouts, ob):
+        assert (o[:b] == O.float_compress(FLOAT32, a)).all()
+    fdec = [np.zeros(a.size, np.uint32) for a in fins]
+    O.float_decompress_batch(fouts, fdec)
+    assert all((d == a).all() for d, a in zip(fdec, fins))
