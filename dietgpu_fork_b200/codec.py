@@ -1,0 +1,153 @@
+"""Raw-device-pointer codec API over torch tensors (device memory and streams only).
+
+Mirrors the reference's C++ entry points one to one (same names in snake_case, same argument
+meaning; /root/reference/dietgpu/ans/GpuANSCodec.h, /root/reference/dietgpu/float/GpuFloatCodec.h):
+host-side lists of tensors play the role of the host pointer arrays, `out_sizes` / `out_success`
+are device tensors written asynchronously on the current CUDA stream. Everything runs in
+libdietgpu_b200.so; there is no fallback.
+"""
+import ctypes as C
+
+import torch
+
+from . import _capi
+from ._capi import BFLOAT16, FLOAT16, FLOAT32, FLOAT64, lib
+
+FLOAT_TYPE_OF_DTYPE = {
+    torch.float16: FLOAT16,
+    torch.bfloat16: BFLOAT16,
+    torch.float32: FLOAT32,
+    torch.float64: FLOAT64,
+}
+WORD_BYTES = {FLOAT16: 2, BFLOAT16: 2, FLOAT32: 4, FLOAT64: 8}
+
+
+class ChecksumMismatch(RuntimeError):
+    def __init__(self, indices):
+        super().__init__(f"checksum mismatch in batch elements {indices}")
+        self.indices = indices
+
+
+def _stream(stream):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _temp(temp):
+    if temp is None:
+        return None, 0
+    assert temp.is_cuda and temp.is_contiguous()
+    return C.c_void_p(temp.data_ptr()), temp.numel() * temp.element_size()
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _ptrs(ts):
+    return _capi.ptr_array([t.data_ptr() for t in ts])
+
+
+def get_max_compressed_size(uncompressed_bytes):
+    return lib.dgb_ans_max_compressed_size(uncompressed_bytes)
+
+
+def get_max_float_compressed_size(float_type, size):
+    return lib.dgb_float_max_compressed_size(float_type, size)
+
+
+def get_max_sparse_float_compressed_size(float_type, size):
+    return lib.dgb_sparse_float_max_compressed_size(float_type, size)
+
+
+def last_temp_bytes_used():
+    return lib.dgb_last_temp_bytes_used()
+
+
+def _raise_mismatch(mm, nm):
+    raise ChecksumMismatch([mm[i] for i in range(min(nm.value, len(mm)))])
+
+
+def ans_encode_batch_pointer(ins, outs, out_sizes, prob_bits=10, use_checksum=False, histogram=None,
+                             temp=None, stream=None, in_sizes=None):
+    """ansEncodeBatchPointer. `ins`: cuda tensors viewed as bytes; `in_sizes` defaults to their byte sizes."""
+    n = len(ins)
+    sizes = in_sizes if in_sizes is not None else [t.numel() * t.element_size() for t in ins]
+    tp, tb = _temp(temp)
+    rc = lib.dgb_ans_encode_batch_pointer(tp, tb, prob_bits, int(use_checksum), n, _ptrs(ins),
+                                          _capi.u32_array(sizes), _ptr(histogram), _ptrs(outs),
+                                          _ptr(out_sizes), _stream(stream))
+    _capi.check(rc, "ansEncodeBatchPointer")
+
+
+def ans_decode_batch_pointer(ins, outs, out_success=None, out_sizes=None, prob_bits=10, use_checksum=False,
+                             temp=None, stream=None, out_capacity=None):
+    n = len(ins)
+    caps = out_capacity if out_capacity is not None else [t.numel() * t.element_size() for t in outs]
+    tp, tb = _temp(temp)
+    mm = (C.c_uint32 * max(n, 1))()
+    nm = C.c_uint32(0)
+    rc = lib.dgb_ans_decode_batch_pointer(tp, tb, prob_bits, int(use_checksum), n, _ptrs(ins), _ptrs(outs),
+                                          _capi.u32_array(caps), _ptr(out_success), _ptr(out_sizes),
+                                          _stream(stream), mm, n, C.byref(nm))
+    if _capi.check(rc, "ansDecodeBatchPointer"):
+        _raise_mismatch(mm, nm)
+
+
+def float_compress(float_type, ins, outs, out_sizes, prob_bits=10, use_checksum=False, temp=None,
+                   stream=None, in_sizes=None):
+    """floatCompress. Sizes are in float words."""
+    n = len(ins)
+    sizes = in_sizes if in_sizes is not None else [t.numel() for t in ins]
+    tp, tb = _temp(temp)
+    rc = lib.dgb_float_compress(tp, tb, float_type, prob_bits, int(use_checksum), n, _ptrs(ins),
+                                _capi.u32_array(sizes), _ptrs(outs), _ptr(out_sizes), _stream(stream))
+    _capi.check(rc, "floatCompress")
+
+
+def float_decompress(float_type, ins, outs, out_success=None, out_sizes=None, prob_bits=10,
+                     use_checksum=False, temp=None, stream=None, out_capacity=None):
+    n = len(ins)
+    caps = out_capacity if out_capacity is not None else [t.numel() for t in outs]
+    tp, tb = _temp(temp)
+    mm = (C.c_uint32 * max(n, 1))()
+    nm = C.c_uint32(0)
+    rc = lib.dgb_float_decompress(tp, tb, float_type, prob_bits, int(use_checksum), n, _ptrs(ins),
+                                  _ptrs(outs), _capi.u32_array(caps), _ptr(out_success), _ptr(out_sizes),
+                                  _stream(stream), mm, n, C.byref(nm))
+    if _capi.check(rc, "floatDecompress"):
+        _raise_mismatch(mm, nm)
+
+
+def float_compress_sparse(float_type, ins, outs, out_sizes, prob_bits=10, temp=None, stream=None,
+                          in_sizes=None):
+    n = len(ins)
+    sizes = in_sizes if in_sizes is not None else [t.numel() for t in ins]
+    tp, tb = _temp(temp)
+    rc = lib.dgb_float_compress_sparse(tp, tb, float_type, prob_bits, 0, n, _ptrs(ins),
+                                       _capi.u32_array(sizes), _ptrs(outs), _ptr(out_sizes),
+                                       _stream(stream))
+    _capi.check(rc, "floatCompressSparse")
+
+
+def float_decompress_sparse(float_type, ins, outs, out_success=None, out_sizes=None, prob_bits=10,
+                            temp=None, stream=None, out_capacity=None):
+    n = len(ins)
+    caps = out_capacity if out_capacity is not None else [t.numel() for t in outs]
+    tp, tb = _temp(temp)
+    rc = lib.dgb_float_decompress_sparse(tp, tb, float_type, prob_bits, 0, n, _ptrs(ins), _ptrs(outs),
+                                         _capi.u32_array(caps), _ptr(out_success), _ptr(out_sizes),
+                                         _stream(stream))
+    _capi.check(rc, "floatDecompressSparse")
+
+
+def ans_get_compressed_info(ins, out_sizes=None, out_checksum=None, stream=None):
+    rc = lib.dgb_ans_get_compressed_info(_ptrs(ins), 0, len(ins), _ptr(out_sizes), _ptr(out_checksum),
+                                         None, 0, _stream(stream))
+    _capi.check(rc, "ansGetCompressedInfo")
+
+
+def float_get_compressed_info(ins, out_sizes=None, out_types=None, out_checksum=None, stream=None):
+    rc = lib.dgb_float_get_compressed_info(_ptrs(ins), 0, len(ins), _ptr(out_sizes), _ptr(out_types),
+                                           _ptr(out_checksum), None, 0, _stream(stream))
+    _capi.check(rc, "floatGetCompressedInfo")

@@ -1,0 +1,249 @@
+// Sparse-float bitmap build / compaction and its inverse for sm_100a.
+//
+// Archive (dietgpu/float/GpuFloatUtils.cuh:98-128, GpuSparseFloatCompress.cuh:29-247):
+//   [0,16)  u32 size = N (+12 bytes the reference leaves undefined, 0 here)
+//   [16, 16 + roundUp(ceil(N/8),16))  bitmap, bit (7 - i%8) of byte i/8 = (word i != 0 as an integer)
+//   then a complete float archive of the non-zero words in index order.
+// The reference builds a byte-per-word bitmap, packs it, runs thrust::exclusive_scan per batch
+// element on the default stream between two device synchronisations, and scatters with a u32
+// index array. Here a single persistent kernel per direction does it on the caller's stream:
+// every warp holds 32 steps x 32 words in registers, one ballot per step is the packed bitmap,
+// popc gives the counts, and the tile's output offset comes from a decoupled look-back.
+#include "internal.h"
+
+namespace dgb {
+
+constexpr uint32_t kSpSteps = 32;                        // steps of 32 words per warp
+constexpr uint32_t kSpWarpWords = kSpSteps * 32;         // 1024
+constexpr uint32_t kSpTileWords = kSpWarpWords * 8;      // 8192 words per CTA tile
+
+struct SparseParams {
+  const Elem* elems;   // tiles sized with kSpTileWords
+  uint32_t numElems;
+  uint32_t totalTiles;
+  uint8_t* dense;      // dense rows at dense + planeOff * wordBytes
+  uint32_t* nnz;       // [numElems]
+  unsigned long long* tileState;
+  uint32_t* ticket;
+  uint32_t* errFlag;
+  uint8_t* outSuccess; // scatter only, nullable
+  uint32_t* outSize;   // scatter only, nullable
+};
+
+// ballot (bit l = lane l) -> the 4 bitmap bytes of these 32 words as a little-endian u32
+__device__ __forceinline__ uint32_t ballotToBitmap(uint32_t b) { return __byte_perm(__brev(b), 0, 0x0123); }
+__device__ __forceinline__ uint32_t bitmapToBallot(uint32_t w) { return __brev(__byte_perm(w, 0, 0x0123)); }
+
+template <typename Word>
+__global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
+  __shared__ uint32_t sTicket, sElem, sExcl;
+  __shared__ uint32_t sWarpTot[8];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t ltMask = laneMaskLt();
+  uint32_t guess = 0;
+  while (true) {
+    if (tid == 0) {
+      uint32_t tk = atomicAdd(p.ticket, 1u);
+      sTicket = tk;
+      if (tk < p.totalTiles) sElem = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tk, guess);
+    }
+    __syncthreads();
+    const uint32_t tk = sTicket;
+    if (tk >= p.totalTiles) break;
+    const uint32_t e = sElem;
+    guess = e;
+    const Elem el = p.elems[e];
+    const uint32_t t = tk - el.tileBase;
+    const uint32_t n = el.n;
+    const uint32_t numTiles = max(1u, divUp(n, kSpTileWords));
+    const Word* in = (const Word*)el.in;
+    uint8_t* out = (uint8_t*)el.out;
+    uint32_t* bitmap = (uint32_t*)(out + 16);
+    Word* dense = (Word*)p.dense + el.planeOff;
+
+    // ---- load 32 steps of 32 words, one ballot per step ----
+    const uint32_t wbase = t * kSpTileWords + w * kSpWarpWords;
+    Word v[kSpSteps];
+#pragma unroll
+    for (uint32_t k = 0; k < kSpSteps; ++k) {
+      uint32_t i = wbase + k * 32 + lane;
+      v[k] = i < n ? in[i] : Word(0);
+    }
+    uint32_t myBallot = 0; // lane k keeps the ballot of step k
+#pragma unroll
+    for (uint32_t k = 0; k < kSpSteps; ++k) {
+      uint32_t b = __ballot_sync(0xffffffffu, v[k] != Word(0));
+      if (lane == k) myBallot = b;
+    }
+    const uint32_t myCount = __popc(myBallot);
+    uint32_t inc = myCount; // inclusive scan over steps
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (uint32_t)o) inc += x;
+    }
+    if (lane == 31) sWarpTot[w] = inc;
+    // bitmap words of this warp: step k covers words [wbase + 32k, +32) -> bitmap u32 index (wbase/32 + k)
+    {
+      uint32_t stepWord = wbase + lane * 32;
+      if (stepWord < roundUp(n, 32)) bitmap[stepWord >> 5] = ballotToBitmap(myBallot);
+    }
+    __syncthreads();
+    uint32_t warpOff = 0, tileTot = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j) {
+      uint32_t x = sWarpTot[j];
+      warpOff += j < w ? x : 0u;
+      tileTot += x;
+    }
+    if (w == 0) {
+      uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileTot, p.errFlag);
+      if (lane == 0) sExcl = ex;
+    }
+    __syncthreads();
+    const uint32_t excl = sExcl;
+    const uint32_t stepOff = excl + warpOff + inc - myCount; // lane k: where step k's non-zeros start
+#pragma unroll
+    for (uint32_t k = 0; k < kSpSteps; ++k) {
+      uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
+      uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
+      if ((b >> lane) & 1u) dense[o + __popc(b & ltMask)] = v[k];
+    }
+    if (t == 0 && tid == 0) ((uint4*)out)[0] = make_uint4(n, 0u, 0u, 0u); // GpuSparseFloatHeader
+    if (t == numTiles - 1) {
+      if (tid == 0) p.nnz[e] = excl + tileTot;
+      // zero the bitmap padding up to its 16-byte boundary
+      uint32_t firstPad = roundUp(n, 32) >> 5, endPad = sparseBitmapBytes(n) >> 2;
+      if (firstPad + tid < endPad) bitmap[firstPad + tid] = 0;
+    }
+  }
+}
+
+template <typename Word>
+__global__ void __launch_bounds__(256) k_sparseScatter(const SparseParams p) {
+  __shared__ uint32_t sTicket, sElem, sExcl;
+  __shared__ uint32_t sWarpTot[8];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t ltMask = laneMaskLt();
+  uint32_t guess = 0;
+  while (true) {
+    if (tid == 0) {
+      uint32_t tk = atomicAdd(p.ticket, 1u);
+      sTicket = tk;
+      if (tk < p.totalTiles) sElem = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tk, guess);
+    }
+    __syncthreads();
+    const uint32_t tk = sTicket;
+    if (tk >= p.totalTiles) break;
+    const uint32_t e = sElem;
+    guess = e;
+    const Elem el = p.elems[e];
+    const uint32_t t = tk - el.tileBase;
+    const uint8_t* arch = (const uint8_t*)el.in;
+    const uint32_t n = *(const uint32_t*)arch; // total words
+    const bool ok = el.n >= n;                 // capacity
+    if (t == 0 && tid == 0) {
+      // dietgpu/float/GpuSparseFloatDecompress.cuh:119-121: the reported size is the total N
+      if (p.outSuccess) p.outSuccess[e] = ok ? 1 : 0;
+      if (p.outSize) p.outSize[e] = n;
+    }
+    if (!ok || t >= divUp(n, kSpTileWords)) {
+      __syncthreads();
+      continue;
+    }
+    const uint32_t* bitmap = (const uint32_t*)(arch + 16);
+    const Word* dense = (const Word*)p.dense + el.planeOff;
+    Word* out = (Word*)el.out;
+
+    const uint32_t wbase = t * kSpTileWords + w * kSpWarpWords;
+    const uint32_t stepWord = wbase + lane * 32;
+    uint32_t myBallot = 0;
+    if (stepWord < n) myBallot = bitmapToBallot(bitmap[stepWord >> 5]);
+    const uint32_t myCount = __popc(myBallot);
+    uint32_t inc = myCount;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (uint32_t)o) inc += x;
+    }
+    if (lane == 31) sWarpTot[w] = inc;
+    __syncthreads();
+    uint32_t warpOff = 0, tileTot = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j) {
+      uint32_t x = sWarpTot[j];
+      warpOff += j < w ? x : 0u;
+      tileTot += x;
+    }
+    if (w == 0) {
+      uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileTot, p.errFlag);
+      if (lane == 0) sExcl = ex;
+    }
+    __syncthreads();
+    const uint32_t stepOff = sExcl + warpOff + inc - myCount;
+#pragma unroll 8
+    for (uint32_t k = 0; k < kSpSteps; ++k) {
+      uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
+      uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
+      uint32_t i = wbase + k * 32 + lane;
+      Word val = Word(0);
+      if ((b >> lane) & 1u) val = dense[o + __popc(b & ltMask)];
+      if (i < n) out[i] = val;
+    }
+  }
+}
+
+static void sparseParams(SparseParams& p, Temp& tmp, const Elem* elems, uint32_t numElems, uint32_t totalTiles) {
+  size_t zeroBytes = (size_t)totalTiles * 8 + 16;
+  uint8_t* zero = (uint8_t*)tmp.alloc(zeroBytes);
+  p.elems = elems;
+  p.numElems = numElems;
+  p.totalTiles = totalTiles;
+  p.tileState = (unsigned long long*)zero;
+  p.ticket = zero ? (uint32_t*)(zero + (size_t)totalTiles * 8) : nullptr;
+  p.errFlag = zero ? p.ticket + 1 : nullptr;
+  p.outSuccess = nullptr;
+  p.outSize = nullptr;
+}
+
+int launchSparseCompact(Temp& tmp, int ft, const Elem* elems, uint32_t numElems, uint32_t totalTiles,
+                        uint8_t* dense, uint32_t* nnz, cudaStream_t s) {
+  if (!numElems) return kOk;
+  SparseParams p;
+  sparseParams(p, tmp, elems, numElems, totalTiles);
+  if (tmp.failed()) return kErrCuda;
+  p.dense = dense;
+  p.nnz = nnz;
+  DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
+  uint32_t grid = min(totalTiles, (uint32_t)smCount() * 4u);
+  switch (floatWordBytes(ft)) {
+    case 2: k_sparseCompact<uint16_t><<<grid, 256, 0, s>>>(p); break;
+    case 4: k_sparseCompact<uint32_t><<<grid, 256, 0, s>>>(p); break;
+    default: k_sparseCompact<unsigned long long><<<grid, 256, 0, s>>>(p); break;
+  }
+  DGB_CUDA(cudaGetLastError());
+  return kOk;
+}
+
+int launchSparseScatter(Temp& tmp, int ft, const Elem* elems, uint32_t numElems, uint32_t totalTiles,
+                        const uint8_t* dense, uint8_t* outSuccess, uint32_t* outSize, cudaStream_t s) {
+  if (!numElems) return kOk;
+  SparseParams p;
+  sparseParams(p, tmp, elems, numElems, totalTiles);
+  if (tmp.failed()) return kErrCuda;
+  p.dense = (uint8_t*)dense;
+  p.nnz = nullptr;
+  p.outSuccess = outSuccess;
+  p.outSize = outSize;
+  DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
+  uint32_t grid = min(totalTiles, (uint32_t)smCount() * 4u);
+  switch (floatWordBytes(ft)) {
+    case 2: k_sparseScatter<uint16_t><<<grid, 256, 0, s>>>(p); break;
+    case 4: k_sparseScatter<uint32_t><<<grid, 256, 0, s>>>(p); break;
+    default: k_sparseScatter<unsigned long long><<<grid, 256, 0, s>>>(p); break;
+  }
+  DGB_CUDA(cudaGetLastError());
+  return kOk;
+}
+
+} // namespace dgb

@@ -1,0 +1,161 @@
+/*
+ * dietgpu_b200.h — C ABI of libdietgpu_b200.so, the B200-native (sm_100a) DietGPU codec.
+ *
+ * Every entry point is the C face of one function of the reference's C++ API
+ * (namespace dietgpu, /root/reference/dietgpu/ans/GpuANSCodec.h and
+ * /root/reference/dietgpu/float/GpuFloatCodec.h); argument meaning, units and host/device
+ * placement are the reference's:
+ *   - `in`, `in_size`, `out`, `out_capacity`, split-size arrays: HOST arrays, read during the call;
+ *   - `*_dev`: DEVICE arrays, written asynchronously on `stream`;
+ *   - ANS sizes are bytes; float sizes / capacities / out sizes are float WORDS; compressed
+ *     sizes are always bytes;
+ *   - everything is enqueued on `stream` (a cudaStream_t) of the current device; calls return
+ *     without synchronising, except decode with use_checksum != 0 (the reference blocks there
+ *     too, dietgpu/ans/GpuANSDecode.cuh:558-591).
+ * The reference's `StackDeviceMemory& res` becomes (`temp_dev`, `temp_bytes`): a caller-owned
+ * device scratch buffer. If it is NULL or too small the library takes the remainder from the
+ * stream-ordered CUDA pool (the reference falls back to cudaMalloc,
+ * dietgpu/utils/StackDeviceMemory.cpp:119-139). include/dietgpu_b200.hpp rebuilds the C++
+ * signatures (StackDeviceMemory, ANSCodecConfig, status structs) on top of this file.
+ *
+ * Archives must be 16-byte aligned (as the reference requires); inputs/outputs need only the
+ * natural alignment of their element type, 16-byte alignment enables the vector paths.
+ *
+ * Return value: 0 = ok, 1 = checksum mismatch (decode only), < 0 = error (DGB_ERR_*).
+ * There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef DIETGPU_B200_H
+#define DIETGPU_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGB_OK 0
+#define DGB_CHECKSUM_MISMATCH 1
+#define DGB_ERR_INVALID_ARG (-1)
+#define DGB_ERR_CUDA (-2)
+#define DGB_ERR_ALIGNMENT (-3)
+#define DGB_ERR_INTERNAL (-4)
+
+/* dietgpu::FloatType, dietgpu/float/GpuFloatCodec.h:18-24 */
+#define DGB_FLOAT16 1
+#define DGB_BFLOAT16 2
+#define DGB_FLOAT32 3
+#define DGB_FLOAT64 4
+
+/* ---- sizes ------------------------------------------------------------------------------ */
+/* getMaxCompressedSize, dietgpu/ans/GpuANSCodec.h:22 (dietgpu/ans/GpuANSEncode.cu:13-25) */
+uint32_t dgb_ans_max_compressed_size(uint32_t uncompressed_bytes);
+/* getMaxFloatCompressedSize, dietgpu/float/GpuFloatCodec.h:27 (GpuFloatCompress.cu:23-48) */
+uint32_t dgb_float_max_compressed_size(int float_type, uint32_t num_words);
+/* getMaxSparseFloatCompressedSize, dietgpu/float/GpuFloatCodec.h:30 (GpuSparseFloatCompress.cu:16-24) */
+uint32_t dgb_sparse_float_max_compressed_size(int float_type, uint32_t num_words);
+/* Upper bound on the scratch an operation takes from temp_dev for a batch of `num_in_batch`
+ * elements of at most `max_size` bytes (ANS) / words (float). op: 0 ans encode, 1 ans decode,
+ * 2 float compress, 3 float decompress, 4 sparse compress, 5 sparse decompress. */
+size_t dgb_temp_bytes_required(int op, int float_type, uint32_t num_in_batch, uint32_t max_size);
+
+/* ---- ANS byte codec --------------------------------------------------------------------- */
+/* ansEncodeBatchPointer, dietgpu/ans/GpuANSCodec.h:157-176 */
+int dgb_ans_encode_batch_pointer(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                 uint32_t num_in_batch, const void* const* in, const uint32_t* in_size,
+                                 const uint32_t* histogram_dev, void* const* out,
+                                 uint32_t* out_size_dev, void* stream);
+/* ansEncodeBatchStride, dietgpu/ans/GpuANSCodec.h:98-131 */
+int dgb_ans_encode_batch_stride(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                uint32_t num_in_batch, const void* in_dev, uint32_t in_per_batch_size,
+                                uint32_t in_per_batch_stride, const uint32_t* histogram_dev,
+                                void* out_dev, uint32_t out_per_batch_stride,
+                                uint32_t* out_batch_size_dev, void* stream);
+/* ansEncodeBatchSplitSize, dietgpu/ans/GpuANSCodec.h:178-214 */
+int dgb_ans_encode_batch_split_size(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                    uint32_t num_in_batch, const void* in_dev,
+                                    const uint32_t* in_split_sizes, const uint32_t* histogram_dev,
+                                    void* out_dev, uint32_t out_stride, uint32_t* out_size_dev,
+                                    void* stream);
+
+/* ansDecodeBatchPointer, dietgpu/ans/GpuANSCodec.h:259-279. On DGB_CHECKSUM_MISMATCH the first
+ * min(*num_mismatch, mismatch_capacity) failing batch indices are stored in mismatch_idx
+ * (both nullable); this replaces ANSDecodeStatus::errorInfo. */
+int dgb_ans_decode_batch_pointer(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                 uint32_t num_in_batch, const void* const* in, void* const* out,
+                                 const uint32_t* out_capacity, uint8_t* out_success_dev,
+                                 uint32_t* out_size_dev, void* stream, uint32_t* mismatch_idx,
+                                 uint32_t mismatch_capacity, uint32_t* num_mismatch);
+/* ansDecodeBatchStride, dietgpu/ans/GpuANSCodec.h:222-257 */
+int dgb_ans_decode_batch_stride(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                uint32_t num_in_batch, const void* in_dev, uint32_t in_per_batch_stride,
+                                void* out_dev, uint32_t out_per_batch_stride,
+                                uint32_t out_per_batch_capacity, uint8_t* out_success_dev,
+                                uint32_t* out_size_dev, void* stream, uint32_t* mismatch_idx,
+                                uint32_t mismatch_capacity, uint32_t* num_mismatch);
+/* ansDecodeBatchSplitSize, dietgpu/ans/GpuANSCodec.h:281-313 */
+int dgb_ans_decode_batch_split_size(void* temp_dev, size_t temp_bytes, int prob_bits, int use_checksum,
+                                    uint32_t num_in_batch, const void* const* in, void* out_dev,
+                                    const uint32_t* out_split_sizes, uint8_t* out_success_dev,
+                                    uint32_t* out_size_dev, void* stream, uint32_t* mismatch_idx,
+                                    uint32_t mismatch_capacity, uint32_t* num_mismatch);
+
+/* ansGetCompressedInfo / ansGetCompressedInfoDevice, dietgpu/ans/GpuANSCodec.h:315-341.
+ * in_is_device != 0: `in` is a device array of device pointers. Outputs nullable. */
+int dgb_ans_get_compressed_info(const void* const* in, int in_is_device, uint32_t num_in_batch,
+                                uint32_t* out_sizes_dev, uint32_t* out_checksum_dev, void* temp_dev,
+                                size_t temp_bytes, void* stream);
+
+/* ---- float codecs ----------------------------------------------------------------------- */
+/* floatCompress, dietgpu/float/GpuFloatCodec.h:105-140 */
+int dgb_float_compress(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                       int use_checksum, uint32_t num_in_batch, const void* const* in,
+                       const uint32_t* in_size, void* const* out, uint32_t* out_size_dev, void* stream);
+/* floatCompressSplitSize, dietgpu/float/GpuFloatCodec.h:142-164 */
+int dgb_float_compress_split_size(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                                  int use_checksum, uint32_t num_in_batch, const void* in_dev,
+                                  const uint32_t* in_split_sizes, void* out_dev, uint32_t out_stride,
+                                  uint32_t* out_size_dev, void* stream);
+/* floatCompressSparse, dietgpu/float/GpuFloatCodec.h:166-176 */
+int dgb_float_compress_sparse(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                              int use_checksum, uint32_t num_in_batch, const void* const* in,
+                              const uint32_t* in_size, void* const* out, uint32_t* out_size_dev,
+                              void* stream);
+
+/* floatDecompress, dietgpu/float/GpuFloatCodec.h:190-224 */
+int dgb_float_decompress(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                         int use_checksum, uint32_t num_in_batch, const void* const* in,
+                         void* const* out, const uint32_t* out_capacity, uint8_t* out_success_dev,
+                         uint32_t* out_size_dev, void* stream, uint32_t* mismatch_idx,
+                         uint32_t mismatch_capacity, uint32_t* num_mismatch);
+/* floatDecompressSplitSize, dietgpu/float/GpuFloatCodec.h:226-260 */
+int dgb_float_decompress_split_size(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                                    int use_checksum, uint32_t num_in_batch, const void* const* in,
+                                    void* out_dev, const uint32_t* out_split_sizes,
+                                    uint8_t* out_success_dev, uint32_t* out_size_dev, void* stream,
+                                    uint32_t* mismatch_idx, uint32_t mismatch_capacity,
+                                    uint32_t* num_mismatch);
+/* floatDecompressSparse, dietgpu/float/GpuFloatCodec.h:262-273 */
+int dgb_float_decompress_sparse(void* temp_dev, size_t temp_bytes, int float_type, int prob_bits,
+                                int use_checksum, uint32_t num_in_batch, const void* const* in,
+                                void* const* out, const uint32_t* out_capacity,
+                                uint8_t* out_success_dev, uint32_t* out_size_dev, void* stream);
+
+/* floatGetCompressedInfo / floatGetCompressedInfoDevice, dietgpu/float/GpuFloatCodec.h:275-322 */
+int dgb_float_get_compressed_info(const void* const* in, int in_is_device, uint32_t num_in_batch,
+                                  uint32_t* out_sizes_dev, uint32_t* out_types_dev,
+                                  uint32_t* out_checksum_dev, void* temp_dev, size_t temp_bytes,
+                                  void* stream);
+
+/* Scratch bytes the last finished call on this thread took (from temp_dev plus the pool): what the
+ * reference reports through StackDeviceMemory::getMaxMemoryUsage(),
+ * dietgpu/utils/StackDeviceMemory.h:196-200. */
+size_t dgb_last_temp_bytes_used(void);
+
+/* library version / build tag, e.g. "dietgpu_b200 r1 sm_100a" */
+const char* dgb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIETGPU_B200_H */

@@ -41,5 +41,5 @@ pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done
 # The reference defines a few non-template __global__ helpers in headers that two of its own
 # shared libraries include (its CMake links them separately); the definitions are identical.
-"$NVCC" -shared -Xlinker --allow-multiple-definition -o "$OUT/libdietgpu_ref.so" "${objs[@]}" -lcudart
+"$NVCC" -shared -Xlinker --allow-multiple-definition -o "$OUT/libdietgpu_ref.so" "${objs[@]}"
 echo "built $OUT/libdietgpu_ref.so"

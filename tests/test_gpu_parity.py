@@ -1,0 +1,197 @@
+"""`-m gpu` parity tests: our CUDA path (through the C ABI) against the CPU oracle byte for byte,
+and against the reference's own CUDA build (oracle/_ref) under the defined-byte mask, plus
+cross-decoding both ways. Sizes / generators follow the reference's tests
+(dietgpu/ans/ANSTest.cu:243-282, dietgpu/float/FloatTest.cu:287-341)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import datagen
+import gpu_harness as H
+
+pytestmark = pytest.mark.gpu
+
+F16, BF16, F32, F64 = 1, 2, 3, 4
+needs_ref = pytest.mark.skipif(H.ref_lib() is None, reason="oracle/_ref/libdietgpu_ref.so not built")
+
+
+def _assert_same(ours, expect, what):
+    assert ours.size == expect.size, f"{what}: size {ours.size} != {expect.size}"
+    if not np.array_equal(ours, expect):
+        bad = np.nonzero(ours != expect)[0]
+        raise AssertionError(f"{what}: {bad.size} bytes differ, first at {bad[:8]}")
+
+
+ANS_SIZES = [[0], [1], [1, 1], [31, 32, 33], [4096, 4095, 4096], [1234, 2345, 3456],
+             [10000, 10013, 10000], [32768, 32769, 65536 + 7], [300000]]
+
+
+@pytest.mark.parametrize("pb", [9, 10, 11])
+@pytest.mark.parametrize("lam", [1.0, 20.0, 1000.0])
+@pytest.mark.parametrize("sizes", ANS_SIZES, ids=lambda s: "x".join(map(str, s)))
+def test_ans_matches_oracle(pb, lam, sizes):
+    host = [datagen.exp_bytes(n, lam, seed=10 + i) for i, n in enumerate(sizes)]
+    for mis in (0, 4):
+        dev = [H.to_dev(h, mis) for h in host]
+        m, sz = H.ours_ans_encode(dev, pb)
+        for i, h in enumerate(host):
+            exp = oracle.ans_encode(h, pb)
+            assert sz[i] % 16 == 0
+            _assert_same(H.row_bytes(m, i, sz[i]), exp, f"ans archive {i} (misalign {mis})")
+        arch = [m[i] for i in range(len(host))]
+        outs, ok, dsz = H.ours_ans_decode(arch, sizes, pb, misalign=mis)
+        assert ok.all() and list(dsz) == list(sizes)
+        for i, h in enumerate(host):
+            _assert_same(outs[i].cpu().numpy(), h, f"ans decode {i}")
+
+
+def test_ans_random_batch_and_checksum():
+    rng = np.random.default_rng(5)
+    sizes = [int(x) for x in rng.integers(100, 10000, 100)]
+    host = [datagen.exp_bytes(n, 10.0, seed=100 + i) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    m, sz = H.ours_ans_encode(dev, 10, checksum=True)
+    for i, h in enumerate(host):
+        _assert_same(H.row_bytes(m, i, sz[i]), oracle.ans_encode(h, 10, use_checksum=True), f"archive {i}")
+    # decode from buffers truncated to the reported size (dietgpu/ans_test.py:21-26)
+    arch = [H.to_dev(H.row_bytes(m, i, sz[i])) for i in range(len(host))]
+    outs, ok, dsz = H.ours_ans_decode(arch, sizes, 10, checksum=True)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h, f"decode {i}")
+
+
+def test_ans_capacity_too_small_and_corrupt_checksum():
+    host = [datagen.exp_bytes(5000, 10.0, seed=1), datagen.exp_bytes(6000, 10.0, seed=2)]
+    dev = [H.to_dev(h) for h in host]
+    m, sz = H.ours_ans_encode(dev, 10, checksum=True)
+    arch = [m[0], m[1]]
+    outs, ok, dsz = H.ours_ans_decode(arch, [5000, 100], 10)
+    assert list(ok) == [1, 0] and list(dsz) == [5000, 6000]
+    _assert_same(outs[0].cpu().numpy(), host[0], "decode 0")
+    from dietgpu_fork_b200.codec import ChecksumMismatch
+    m[1, 20] ^= 0x5A  # header checksum byte
+    with pytest.raises(ChecksumMismatch) as ei:
+        H.ours_ans_decode(arch, [5000, 6000], 10, checksum=True)
+    assert ei.value.indices == [1]
+
+
+FLOAT_SIZES = [[1], [13, 1], [12345, 1, 8083, 1, 17], [16, 32, 48], [32768, 32769, 70001], [0, 5]]
+
+
+@pytest.mark.parametrize("ft", [F16, BF16, F32, F64])
+@pytest.mark.parametrize("pb", [9, 10])
+@pytest.mark.parametrize("sizes", FLOAT_SIZES, ids=lambda s: "x".join(map(str, s)))
+def test_float_matches_oracle(ft, pb, sizes):
+    host = [datagen.float_words(ft, n, seed=10 + i) for i, n in enumerate(sizes)]
+    wb = host[0].dtype.itemsize
+    for mis in (0, wb):
+        dev = [H.to_dev(h, mis) for h in host]
+        m, sz = H.ours_float_compress(ft, dev, sizes, pb)
+        for i, h in enumerate(host):
+            _assert_same(H.row_bytes(m, i, sz[i]), oracle.float_compress(ft, h, pb), f"float archive {i} mis {mis}")
+        arch = [m[i] for i in range(len(host))]
+        outs, ok, dsz = H.ours_float_decompress(ft, arch, sizes, pb, misalign=mis)
+        assert ok.all() and list(dsz) == list(sizes)
+        for i, h in enumerate(host):
+            _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"float decode {i} mis {mis}")
+
+
+@pytest.mark.parametrize("ft", [F16, BF16, F32, F64])
+def test_float_checksum_roundtrip(ft):
+    sizes = [1000, 4097, 20000]
+    host = [datagen.float_words(ft, n, seed=20 + i) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    m, sz = H.ours_float_compress(ft, dev, sizes, 10, checksum=True)
+    for i, h in enumerate(host):
+        _assert_same(H.row_bytes(m, i, sz[i]), oracle.float_compress(ft, h, 10, use_checksum=True), f"archive {i}")
+    outs, ok, dsz = H.ours_float_decompress(ft, [m[i] for i in range(3)], sizes, 10, checksum=True)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"decode {i}")
+
+
+@pytest.mark.parametrize("ft", [F16, BF16, F32, F64])
+@pytest.mark.parametrize("sparsity", [0.0, 0.5, 0.9, 1.0])
+def test_sparse_matches_oracle(ft, sparsity):
+    sizes = [2, 100, 8191, 8193, 100000]
+    host = [datagen.float_words(ft, n, seed=30 + i, sparsity=sparsity) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    m, sz = H.ours_float_compress(ft, dev, sizes, 10, sparse=True)
+    for i, h in enumerate(host):
+        _assert_same(H.row_bytes(m, i, sz[i]), oracle.sparse_float_compress(ft, h, 10), f"sparse archive {i}")
+    outs, ok, dsz = H.ours_float_decompress(ft, [m[i] for i in range(len(sizes))], sizes, 10, sparse=True)
+    assert ok.all() and list(dsz) == list(sizes)
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"sparse decode {i}")
+
+
+# ---------------------------------------------------------------- against the reference CUDA build
+@needs_ref
+@pytest.mark.parametrize("pb", [9, 10, 11])
+def test_ans_matches_reference_build(pb):
+    sizes = [1, 4096, 4095, 10013, 70001, 1 << 20]
+    host = [datagen.exp_bytes(n, 20.0, seed=40 + i) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    mo, so = H.ours_ans_encode(dev, pb)
+    mr, sr = H.ref_ans_encode(dev, pb)
+    assert list(so) == list(sr)
+    for i in range(len(sizes)):
+        a, r = H.row_bytes(mo, i, so[i]), H.row_bytes(mr, i, sr[i])
+        mask = oracle.ans_defined_mask(a)
+        assert np.array_equal(a[mask], r[mask]), f"archive {i} differs from the reference build"
+        assert not a[~mask].any()
+    # cross decode: reference decodes ours, we decode the reference's
+    outs, ok, _ = H.ref_ans_decode([mo[i] for i in range(len(sizes))], sizes, pb)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h, f"ref decode of ours {i}")
+    outs, ok, _ = H.ours_ans_decode([mr[i] for i in range(len(sizes))], sizes, pb)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h, f"our decode of ref {i}")
+
+
+@needs_ref
+@pytest.mark.parametrize("ft", [F16, BF16, F32, F64])
+def test_float_matches_reference_build(ft):
+    sizes = [1, 13, 12345, 8083, 32768, 262144 + 3]
+    host = [datagen.float_words(ft, n, seed=50 + i) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    mo, so = H.ours_float_compress(ft, dev, sizes, 10)
+    mr, sr = H.ref_float_compress(ft, dev, sizes, 10)
+    assert list(so) == list(sr)
+    for i in range(len(sizes)):
+        a, r = H.row_bytes(mo, i, so[i]), H.row_bytes(mr, i, sr[i])
+        mask = oracle.float_defined_mask(a)
+        assert np.array_equal(a[mask], r[mask]), f"float archive {i} differs from the reference build"
+    outs, ok, _ = H.ref_float_decompress(ft, [mo[i] for i in range(len(sizes))], sizes, 10)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"ref decode of ours {i}")
+    outs, ok, _ = H.ours_float_decompress(ft, [mr[i] for i in range(len(sizes))], sizes, 10)
+    assert ok.all()
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"our decode of ref {i}")
+
+
+@needs_ref
+@pytest.mark.parametrize("ft", [F32, F64])
+def test_sparse_matches_reference_build(ft):
+    sizes = [1000, 100000, 300001]
+    host = [datagen.float_words(ft, n, seed=60 + i, sparsity=0.9) for i, n in enumerate(sizes)]
+    dev = [H.to_dev(h) for h in host]
+    mo, so = H.ours_float_compress(ft, dev, sizes, 10, sparse=True)
+    mr, sr = H.ref_float_compress(ft, dev, sizes, 10, sparse=True)
+    assert list(so) == list(sr)
+    for i in range(len(sizes)):
+        a, r = H.row_bytes(mo, i, so[i]), H.row_bytes(mr, i, sr[i])
+        mask = oracle.sparse_float_defined_mask(ft, a)
+        assert np.array_equal(a[mask], r[mask]), f"sparse archive {i} differs from the reference build"
+    outs, ok, _ = H.ref_float_decompress(ft, [mo[i] for i in range(len(sizes))], sizes, 10, sparse=True)
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"ref decode of ours {i}")
+    outs, ok, _ = H.ours_float_decompress(ft, [mr[i] for i in range(len(sizes))], sizes, 10, sparse=True)
+    for i, h in enumerate(host):
+        _assert_same(outs[i].cpu().numpy(), h.view(np.uint8), f"our decode of ref {i}")
