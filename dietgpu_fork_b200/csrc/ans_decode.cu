@@ -13,6 +13,7 @@
 // too (the reference always takes two passes for fp64, GpuFloatDecompress.cuh:932-935).
 #include "float_math.cuh"
 #include "internal.h"
+#include "prof.h"
 
 namespace dgb {
 
@@ -236,7 +237,10 @@ static int launchDecodeKernel(const DecParams& p, uint32_t grid, cudaStream_t s)
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t smemBytes = kPlanes * kTileSyms + kTileBlocks * kStageWords * 2 + (4u << PB);
   DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-  k_decode<PB, FT><<<grid, kThreads, smemBytes, s>>>(p);
+  {
+    ProfScope ps__("k_decode", s);
+    k_decode<PB, FT><<<grid, kThreads, smemBytes, s>>>(p);
+  }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }
@@ -262,7 +266,10 @@ int launchDecode(Temp& tmp, const DecodeArgs& a, cudaStream_t s) {
   uint32_t* ticket = tmp.alloc<uint32_t>(4);
   if (tmp.failed()) return kErrCuda;
   DGB_CUDA(cudaMemsetAsync(ticket, 0, 16, s));
-  k_decodePrep<<<dim3(a.numElems, planes), 256, 0, s>>>(a, info, lut);
+  {
+    ProfScope ps__("k_decodePrep", s);
+    k_decodePrep<<<dim3(a.numElems, planes), 256, 0, s>>>(a, info, lut);
+  }
   DGB_CUDA(cudaGetLastError());
   DecParams p;
   p.a = a;

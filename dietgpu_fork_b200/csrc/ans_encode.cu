@@ -12,6 +12,7 @@
 // output offset with a decoupled look-back over tile aggregates and writes states, block index
 // and payload straight to their final place; the last tile of an element writes the header.
 #include "internal.h"
+#include "prof.h"
 
 namespace dgb {
 
@@ -118,7 +119,10 @@ int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, u
   uint32_t ctas = min(totalTiles, (uint32_t)smCount() * 4u);
   uint32_t per = divUp(totalTiles, ctas);
   ctas = divUp(totalTiles, per);
-  k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist);
+  {
+    ProfScope ps__("k_histBytes", s);
+    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist);
+  }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }
@@ -171,7 +175,10 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
   uint32_t perElem = (uint32_t)min((size_t)divUp((uint32_t)smCount() * 8u, numElems),
                                    (maxBytes + 65535) / 65536);
   if (perElem < 1) perElem = 1;
-  k_checksum<<<dim3(perElem, numElems), 256, 0, s>>>(elems, bytesPerUnit, nDev, useOut, checksum);
+  {
+    ProfScope ps__("k_checksum", s);
+    k_checksum<<<dim3(perElem, numElems), 256, 0, s>>>(elems, bytesPerUnit, nDev, useOut, checksum);
+  }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }
@@ -452,7 +459,10 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
   uint8_t* zero = (uint8_t*)tmp.alloc(zeroBytes);
   if (tmp.failed()) return kErrCuda;
   DGB_CUDA(cudaMemsetAsync(zero, 0, zeroBytes, s));
-  k_normalize<<<a.numElems, 256, 0, s>>>(a.elems, a.nDev, a.hist, a.probBits, table);
+  {
+    ProfScope ps__("k_normalize", s);
+    k_normalize<<<a.numElems, 256, 0, s>>>(a.elems, a.nDev, a.hist, a.probBits, table);
+  }
   DGB_CUDA(cudaGetLastError());
 
   EncParams p;
@@ -464,7 +474,10 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
   uint32_t grid = min(a.totalTiles, (uint32_t)smCount() * 2u);
   auto launch = [&](auto kern) -> int {
     DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEncSmem));
-    kern<<<grid, kThreads, kEncSmem, s>>>(p);
+    {
+      ProfScope ps__("k_encode", s);
+      kern<<<grid, kThreads, kEncSmem, s>>>(p);
+    }
     DGB_CUDA(cudaGetLastError());
     return kOk;
   };

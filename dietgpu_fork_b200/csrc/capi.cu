@@ -10,6 +10,7 @@
 
 #include "../../include/dietgpu_b200.h"
 #include "internal.h"
+#include "prof.h"
 
 namespace dgb {
 
@@ -91,7 +92,10 @@ int verifyChecksums(Temp& tmp, const Elem* elemsDev, uint32_t num, uint32_t maxU
   // dietgpu/ans/GpuChecksum.cuh:95-102), mirroring what compression checksummed.
   int rc = launchChecksum(elemsDev, num, maxUnits, 1, sizeDev, 1, computed, s);
   if (rc) return rc;
-  k_verifyChecksum<<<divUp(num, 128), 128, 0, s>>>(elemsDev, num, floatMode, computed, successDev, flags);
+  {
+    ProfScope ps__("k_verifyChecksum", s);
+    k_verifyChecksum<<<divUp(num, 128), 128, 0, s>>>(elemsDev, num, floatMode, computed, successDev, flags);
+  }
   DGB_CUDA(cudaGetLastError());
   std::vector<uint8_t> host(num);
   DGB_CUDA(cudaMemcpyAsync(host.data(), flags, num, cudaMemcpyDeviceToHost, s));
@@ -385,7 +389,10 @@ int getInfo(const void* const* in, int inIsDevice, uint32_t num, int floatMode, 
     DGB_CUDA(cudaMemcpyAsync(d, in, sizeof(void*) * num, cudaMemcpyHostToDevice, s));
     inDev = d;
   }
-  k_info<<<divUp(num, 128), 128, 0, s>>>(inDev, num, floatMode, sizes, types, checksums);
+  {
+    ProfScope ps__("k_info", s);
+    k_info<<<divUp(num, 128), 128, 0, s>>>(inDev, num, floatMode, sizes, types, checksums);
+  }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }

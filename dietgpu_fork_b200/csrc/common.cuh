@@ -123,7 +123,7 @@ __device__ __forceinline__ uint32_t lookbackExclusive(unsigned long long* ts, ui
     if (my >= 0) v = tsLoad(ts + my);
     // wait until all 32 examined tiles are published
     while (__any_sync(0xffffffffu, (v >> 62) == 0)) {
-      if (++spins > (1u << 24)) {
+      if (++spins > (1u << 20)) {
         if (lane == 0 && errFlag) atomicExch(errFlag, 1u);
         break;
       }
@@ -139,7 +139,7 @@ __device__ __forceinline__ uint32_t lookbackExclusive(unsigned long long* ts, ui
     }
     excl += warpSum(val);
     idx -= 32;
-    if (spins > (1u << 24)) break;
+    if (spins > (1u << 20)) break;
   }
   if (lane == 0) tsStore(ts + t, kTsPrefix | (excl + mine));
   return excl;

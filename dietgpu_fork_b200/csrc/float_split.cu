@@ -8,6 +8,7 @@
 // replicated shared-memory bins, and all padding the reference leaves undefined is written as 0.
 #include "float_math.cuh"
 #include "internal.h"
+#include "prof.h"
 
 namespace dgb {
 
@@ -181,7 +182,10 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
   uint32_t ctas = min(p.totalTiles, (uint32_t)smCount() * (FT == kFtF64 ? 3u : 6u));
   p.tilesPerCta = divUp(p.totalTiles, ctas);
   ctas = divUp(p.totalTiles, p.tilesPerCta);
-  k_floatSplit<FT><<<ctas, 256, smemBytes, s>>>(p);
+  {
+    ProfScope ps__("k_floatSplit", s);
+    k_floatSplit<FT><<<ctas, 256, smemBytes, s>>>(p);
+  }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }

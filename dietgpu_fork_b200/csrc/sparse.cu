@@ -10,6 +10,7 @@
 // every warp holds 32 steps x 32 words in registers, one ballot per step is the packed bitmap,
 // popc gives the counts, and the tile's output offset comes from a decoupled look-back.
 #include "internal.h"
+#include "prof.h"
 
 namespace dgb {
 
@@ -103,15 +104,24 @@ __global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
     __syncthreads();
     const uint32_t excl = sExcl;
     const uint32_t stepOff = excl + warpOff + inc - myCount; // lane k: where step k's non-zeros start
+    // Reference quirk (GpuSparseFloatCompress.cuh:163-183): the last word goes to idx[N-2] + 1 and
+    // nnz = idx[N-2] + bitmap[N-1] + 1, i.e. word N-2 is assumed non-zero. When it is zero the
+    // dense array has one extra slot (never written by the reference; 0 here) before the last word.
+    const bool quirk = n >= 2 && in[n - 2] == Word(0);
 #pragma unroll
     for (uint32_t k = 0; k < kSpSteps; ++k) {
       uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
       uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
-      if ((b >> lane) & 1u) dense[o + __popc(b & ltMask)] = v[k];
+      uint32_t dst = o + __popc(b & ltMask);
+      if (quirk && wbase + k * 32 + lane == n - 1) {
+        dense[dst] = Word(0);
+        dst += 1;
+      }
+      if ((b >> lane) & 1u) dense[dst] = v[k];
     }
     if (t == 0 && tid == 0) ((uint4*)out)[0] = make_uint4(n, 0u, 0u, 0u); // GpuSparseFloatHeader
     if (t == numTiles - 1) {
-      if (tid == 0) p.nnz[e] = excl + tileTot;
+      if (tid == 0) p.nnz[e] = excl + tileTot + (quirk ? 1u : 0u);
       // zero the bitmap padding up to its 16-byte boundary
       uint32_t firstPad = roundUp(n, 32) >> 5, endPad = sparseBitmapBytes(n) >> 2;
       if (firstPad + tid < endPad) bitmap[firstPad + tid] = 0;
@@ -181,13 +191,16 @@ __global__ void __launch_bounds__(256) k_sparseScatter(const SparseParams p) {
     }
     __syncthreads();
     const uint32_t stepOff = sExcl + warpOff + inc - myCount;
+    // the last word lives at idx[N-2] + 1 whatever word N-2 was (GpuSparseFloatDecompress.cuh:127-144)
+    bool quirk = false;
+    if (n >= 2) quirk = ((((const uint8_t*)bitmap)[(n - 2) >> 3] >> (7 - ((n - 2) & 7))) & 1u) == 0;
 #pragma unroll 8
     for (uint32_t k = 0; k < kSpSteps; ++k) {
       uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
       uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
       uint32_t i = wbase + k * 32 + lane;
       Word val = Word(0);
-      if ((b >> lane) & 1u) val = dense[o + __popc(b & ltMask)];
+      if ((b >> lane) & 1u) val = dense[o + __popc(b & ltMask) + ((quirk && i == n - 1) ? 1u : 0u)];
       if (i < n) out[i] = val;
     }
   }
@@ -216,6 +229,7 @@ int launchSparseCompact(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
   p.nnz = nnz;
   DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
   uint32_t grid = min(totalTiles, (uint32_t)smCount() * 4u);
+  ProfScope ps__("k_sparseCompact", s);
   switch (floatWordBytes(ft)) {
     case 2: k_sparseCompact<uint16_t><<<grid, 256, 0, s>>>(p); break;
     case 4: k_sparseCompact<uint32_t><<<grid, 256, 0, s>>>(p); break;
@@ -237,6 +251,7 @@ int launchSparseScatter(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
   p.outSize = outSize;
   DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
   uint32_t grid = min(totalTiles, (uint32_t)smCount() * 4u);
+  ProfScope ps__("k_sparseScatter", s);
   switch (floatWordBytes(ft)) {
     case 2: k_sparseScatter<uint16_t><<<grid, 256, 0, s>>>(p); break;
     case 4: k_sparseScatter<uint32_t><<<grid, 256, 0, s>>>(p); break;

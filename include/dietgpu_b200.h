@@ -152,6 +152,15 @@ int dgb_float_get_compressed_info(const void* const* in, int in_is_device, uint3
  * dietgpu/utils/StackDeviceMemory.h:196-200. */
 size_t dgb_last_temp_bytes_used(void);
 
+/* ---- launch accounting (bench.py) --------------------------------------------------------- */
+/* Total kernel launches the library has enqueued in this process. */
+unsigned long long dgb_profile_launches(void);
+/* When enabled, every launch is bracketed by CUDA events on its stream. */
+void dgb_profile_enable(int on);
+/* Waits for the recorded launches and writes "kernel count total_ms\n" lines into buf; clears the
+ * records; returns the number of distinct kernels. */
+int dgb_profile_report(char* buf, size_t cap);
+
 /* library version / build tag, e.g. "dietgpu_b200 r1 sm_100a" */
 const char* dgb_version(void);
 

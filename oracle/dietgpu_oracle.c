@@ -515,19 +515,27 @@ static int word_is_nonzero(int ft, const void* in, uint32_t i) {
 
 /* Archive: u32 size + 12 pad | bitmap roundUp(ceil(N/8),16), MSB-first
  * (dietgpu/float/GpuSparseFloatCompress.cuh:108-110) | float archive of the non-zero words.
- * The reference is undefined for N < 2 (:163, :177-183); this restatement defines it the
- * obvious way. */
+ *
+ * Quirk kept from the reference (GpuSparseFloatCompress.cuh:163-183, mirrored by the decoder at
+ * GpuSparseFloatDecompress.cuh:127-144): the exclusive scan stops one element short, and the last
+ * word is placed at idx[N-2] + 1 with nnz = idx[N-2] + bitmap[N-1] + 1, which assumes word N-2 is
+ * non-zero. When word N-2 IS zero the dense array therefore has one extra slot (at index
+ * idx[N-2]) that the reference never writes (uninitialised temp memory); this restatement
+ * writes 0 there. The reference is undefined for N < 2 (reads index -1); here N < 2 is plain
+ * compaction. */
 uint32_t dgo_sparse_float_compress(int ft, const void* in, uint32_t n, int pb,
                                    int use_checksum, uint8_t* out) {
   uint32_t wb = dgo_float_word_bytes(ft);
   uint32_t bm = round_up((n + 7) / 8, 16);
   memset(out, 0, 16u + bm);
   put32(out, n);
-  uint8_t* nz = (uint8_t*)malloc((size_t)n * wb + 16);
+  uint8_t* nz = (uint8_t*)calloc((size_t)n * wb + 32, 1);
   uint32_t nnz = 0;
   for (uint32_t i = 0; i < n; ++i) {
-    if (word_is_nonzero(ft, in, i)) {
-      out[16 + (i >> 3)] |= (uint8_t)(0x80u >> (i & 7));
+    int b = word_is_nonzero(ft, in, i);
+    if (b) out[16 + (i >> 3)] |= (uint8_t)(0x80u >> (i & 7));
+    if (n >= 2 && i == n - 2 && !b) { ++nnz; continue; } /* the never-written slot (0 here) */
+    if (b) {
       memcpy(nz + (size_t)nnz * wb, (const uint8_t*)in + (size_t)i * wb, wb);
       ++nnz;
     }
@@ -552,7 +560,13 @@ int dgo_sparse_float_decompress(int ft, const uint8_t* a, void* out, uint32_t ca
   uint32_t k = 0;
   for (uint32_t i = 0; i < n; ++i) {
     uint8_t* dst = (uint8_t*)out + (size_t)i * wb;
-    if (a[16 + (i >> 3)] & (0x80u >> (i & 7))) {
+    int bit = (a[16 + (i >> 3)] & (0x80u >> (i & 7))) != 0;
+    /* the last word lives at idx[N-2] + 1 whatever word N-2 was (:127-144) */
+    if (n >= 2 && i == n - 1) {
+      int b2 = (a[16 + ((n - 2) >> 3)] & (0x80u >> ((n - 2) & 7))) != 0;
+      if (!b2) ++k;
+    }
+    if (bit) {
       memcpy(dst, nz + (size_t)k * wb, wb);
       ++k;
     } else {
@@ -563,6 +577,8 @@ int dgo_sparse_float_decompress(int ft, const uint8_t* a, void* out, uint32_t ca
   return 1;
 }
 
+/* When word N-2 is zero the reference's nested float archive depends on an uninitialised word
+ * (see above): only the sparse header and the bitmap are then defined. */
 uint32_t dgo_sparse_float_defined_mask(int ft, const uint8_t* a, uint8_t* mask) {
   (void)ft;
   uint32_t n = get32(a);
@@ -570,7 +586,15 @@ uint32_t dgo_sparse_float_defined_mask(int ft, const uint8_t* a, uint8_t* mask) 
   memset(mask, 0, 16u + bm);
   memset(mask, 1, 4);
   memset(mask + 16, 1, (n + 7) / 8);
-  return 16u + bm + dgo_float_defined_mask(a + 16 + bm, mask + 16 + bm);
+  uint32_t inner = dgo_float_defined_mask(a + 16 + bm, mask + 16 + bm);
+  if (n >= 2) {
+    int b2 = (a[16 + ((n - 2) >> 3)] & (0x80u >> ((n - 2) & 7))) != 0;
+    if (!b2) {
+      memset(mask + 16 + bm, 0, inner);
+      memset(mask + 16 + bm, 1, 8); /* magic + nnz stay defined */
+    }
+  }
+  return 16u + bm + inner;
 }
 
 /* -------------------------------------------- batched drivers (CPU baseline) */

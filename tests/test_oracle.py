@@ -201,7 +201,11 @@ def test_sparse_round_trip(ft, sparsity):
         ok, sz, out = O.sparse_float_decompress(ft, a)
         assert ok and sz == n and (out == w).all()
         m = O.sparse_float_defined_mask(ft, a)
-        assert m.size == a.size and (a[~m] == 0).all()
+        assert m.size == a.size
+        # when word N-2 is zero the reference's nested archive depends on an uninitialised
+        # word (oracle/dietgpu_oracle.c, sparse quirk): it is masked out, not zero
+        if not (n >= 2 and w[n - 2] == 0):
+            assert (a[~m] == 0).all()
 
 
 def test_sparse_bitmap_msb_first_and_negative_zero():
@@ -210,7 +214,14 @@ def test_sparse_bitmap_msb_first_and_negative_zero():
     w[9] = 0x80000000  # -0.0 is "non-zero" (integer compare)
     a = O.sparse_float_compress(FLOAT32, w)
     assert a[16] == 0x80 and a[17] == 0x40
-    assert a[16 + 16 + 4:16 + 16 + 8].view(np.uint32)[0] == 2  # embedded float archive: nnz
+    # embedded float archive: nnz = 2 true non-zeros + the slot the reference never writes because
+    # word N-2 is zero (GpuSparseFloatCompress.cuh:177-183)
+    assert a[16 + 16 + 4:16 + 16 + 8].view(np.uint32)[0] == 3
+    w[14] = 0x40000000  # word N-2 non-zero: plain compaction
+    a = O.sparse_float_compress(FLOAT32, w)
+    assert a[16 + 16 + 4:16 + 16 + 8].view(np.uint32)[0] == 3
+    ok, sz, out = O.sparse_float_decompress(FLOAT32, a)
+    assert ok and (out == w).all()
 
 
 # ---- batched drivers agree with the single-archive entry points ------------------------
