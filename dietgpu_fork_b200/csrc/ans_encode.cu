@@ -189,8 +189,11 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
 // symbol s throughout. Instead of physically sorting we compute each symbol's rank in the
 // descending order of (q << 16 | s): the reference's "positions" are these ranks.
 //
-// Encode-table entry (ours): x = magic, y = pdf | cdf << 12 | shift << 24 with
-// floor(v / pdf) == (umulhi(v, magic) + v) >> shift for v < 2^31.
+// Encode-table entry (ours): x = magic, y = (2^probBits - pdf) | shift << 12 | cdf << 17 with
+// floor(v / pdf) == (umulhi(v, magic) + v) >> shift for v < 2^31. Storing K - pdf serves both the
+// renormalisation test (v >= pdf << (31 - probBits)  <=>  bit 31 of v + ((K - pdf) << (31 - probBits)))
+// and the state update v' = q * (K - pdf) + v + cdf; shift sits where a wrapping funnel shift can
+// take it from y >> 12 without masking. Absent symbols (pdf 0) get an all-zero entry.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elems,
                                                    const uint32_t* __restrict__ nDev,
@@ -261,192 +264,280 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
     uint32_t shift = 32 - __clz(q - 1); // q == 1 -> clz(0) == 32 -> 0
     uint64_t magic = ((1ull << 32) * ((1ull << shift) - q)) / q + 1; // :343-366
     entry.x = (uint32_t)magic;
-    entry.y = q | (cdf << 12) | (shift << 24);
+    entry.y = (weight - q) | (shift << 12) | (cdf << 17);
   }
   table[e * 256 + s] = entry;
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tile encoder
+// Block encoder: one autonomous warp per 4096-symbol ANS block, no CTA-wide barrier anywhere.
+//
+//   ticket (atomicAdd, prefetched one block ahead) -> (element, block)
+//   symbols: 512-byte chunks (16 symbol rows) pulled into a 4-deep per-warp shared-memory ring by
+//            cp.async.bulk (TMA 1-D) + mbarrier, issued 4 chunks ahead of their use
+//   table:   the element's 2 KB encode table, copied into the warp's shared memory when it changes
+//   rows:    rANS step per 32 symbols, ballot/popc compaction into a per-warp staging buffer
+//   offset:  decoupled look-back over the element's per-block aggregates (roundUp(words, 8))
+//   output:  states, index entry and payload written once, at their final place
 // ---------------------------------------------------------------------------------------------
 struct EncParams {
   EncodeArgs a;
-  const uint2* table;           // [numElems][256]
-  unsigned long long* tileState; // [totalTiles], zeroed
-  uint32_t* ticket;             // zeroed
+  const uint2* table;            // [numElems][256]
+  unsigned long long* tileState; // [totalBlocks], zeroed
+  uint32_t* ticket;              // zeroed
   uint32_t* errFlag;
 };
 
-constexpr uint32_t kEncSmem = kTileSyms + 16 + kTileBlocks * kStageWords * 2 + 256 * 8;
+constexpr uint32_t kEncWarps = 4;
+constexpr uint32_t kRingSlots = 4;
+constexpr uint32_t kChunk = 512; // symbols per ring slot = 16 rows
+template <int PB> __host__ __device__ constexpr uint32_t stageBytes() { return PB <= 10 ? 5120u : 5632u; }
+template <int PB> __host__ __device__ constexpr uint32_t encWarpSmem() { return kRingSlots * kChunk + stageBytes<PB>() + 2048u + 64u; }
 
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(bar), "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy (16-byte aligned source, destination and size), completion on `bar`
+__device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+// One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90), table entry already in registers.
 template <int PB>
-__device__ __forceinline__ void encRow(uint32_t& state, uint32_t sym, const uint2* __restrict__ tab,
-                                       uint16_t* __restrict__ stage, uint32_t& off, uint32_t ltMask,
-                                       bool valid) {
-  uint2 e = tab[sym];
-  uint32_t pdf = e.y & 0xfffu;
-  uint32_t cdf = (e.y >> 12) & 0xfffu;
-  uint32_t shift = e.y >> 24;
-  bool wr = valid && state >= (pdf << (31 - PB));
-  uint32_t vote = __ballot_sync(0xffffffffu, wr);
+__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t stageAddr, uint32_t& outBytes,
+                                        uint32_t ltMask) {
+  const bool wr = (int32_t)((e.y << (31 - PB)) + state) < 0; // state >= pdf << (31 - PB)
+  const uint32_t vote = __ballot_sync(0xffffffffu, wr);
   if (wr) {
-    stage[off + __popc(vote & ltMask)] = (uint16_t)state;
+    uint32_t addr = stageAddr + outBytes + 2u * __popc(vote & ltMask);
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)state) : "memory");
     state >>= 16;
   }
-  off += __popc(vote);
-  uint32_t q = (__umulhi(state, e.x) + state) >> shift;
-  uint32_t ns = q * ((1u << PB) - pdf) + state + cdf; // (q << PB) + state % pdf + cdf
+  outBytes += 2u * __popc(vote);
+  const uint32_t q = __funnelshift_r(__umulhi(state, e.x) + state, 0u, e.y >> 12);
+  state = q * (e.y & 0xfffu) + state + (e.y >> 17);
+}
+
+template <int PB>
+__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t stageAddr, uint32_t& outBytes,
+                                               uint32_t ltMask, bool valid) {
+  const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
+  const uint32_t vote = __ballot_sync(0xffffffffu, wr);
+  if (wr) {
+    uint32_t addr = stageAddr + outBytes + 2u * __popc(vote & ltMask);
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)state) : "memory");
+    state >>= 16;
+  }
+  outBytes += 2u * __popc(vote);
+  const uint32_t q = __funnelshift_r(__umulhi(state, e.x) + state, 0u, e.y >> 12);
+  const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
   state = valid ? ns : state;
 }
 
 template <int PB>
-__global__ void __launch_bounds__(256, 2) k_encode(const EncParams p) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  uint8_t* sSym = smem;
-  uint16_t* sStage = (uint16_t*)(smem + kTileSyms + 16);
-  uint2* sTab = (uint2*)(smem + kTileSyms + 16 + kTileBlocks * kStageWords * 2);
-  __shared__ uint32_t sTicket, sElem, sExcl;
-  __shared__ uint32_t sWords[kTileBlocks];
-
-  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+__global__ void __launch_bounds__(kEncWarps * 32, 6) k_encode(const EncParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint8_t* ws = smem + w * encWarpSmem<PB>();
+  uint8_t* ring = ws;                                         // kRingSlots * kChunk
+  uint8_t* stage = ws + kRingSlots * kChunk;                  // stageBytes
+  uint2* tab = (uint2*)(stage + stageBytes<PB>());            // 256 entries
+  const uint32_t bar0 = smemAddr(tab + 256);                  // kRingSlots mbarriers
+  const uint32_t ringAddr = smemAddr(ring), stageAddr = smemAddr(stage), tabAddr = smemAddr(tab);
   const uint32_t ltMask = laneMaskLt();
   const EncodeArgs& a = p.a;
-  uint32_t guess = 0;
 
-  while (true) {
-    if (tid == 0) {
-      uint32_t tk = atomicAdd(p.ticket, 1u);
-      sTicket = tk;
-      if (tk < a.totalTiles) sElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tk, guess);
-    }
-    __syncthreads();
-    const uint32_t tk = sTicket;
-    if (tk >= a.totalTiles) break;
-    const uint32_t e = sElem;
+  if (lane == 0) {
+#pragma unroll
+    for (uint32_t s = 0; s < kRingSlots; ++s) mbarInit(bar0 + 8 * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  uint32_t phaseBits = 0; // parity expected at the next wait on each slot
+
+  // Tickets are taken only when the warp is ready to start the block: a ticket reserved ahead of
+  // time would be a block that later tickets wait on (look-back) while nobody works on it.
+  uint32_t tkLane0 = 0;
+  if (lane == 0) tkLane0 = atomicAdd(p.ticket, 1u);
+  uint32_t tk = __shfl_sync(0xffffffffu, tkLane0, 0);
+  uint32_t curElem = 0xffffffffu, guess = 0;
+
+  while (tk < a.totalTiles) {
+
+    const uint32_t e = findElement(&a.elems[0].blockBase, sizeof(Elem) / 4, a.numElems, tk, guess);
     guess = e;
     const Elem el = a.elems[e];
-    const uint32_t t = tk - el.tileBase;
+    const uint32_t blk = tk - el.blockBase;
     const uint32_t n = a.nDev ? a.nDev[e] : el.n;
     const uint32_t nb = divUp(n, kBlockSyms);
-    const uint32_t numTiles = max(1u, divUp(nb, kTileBlocks));
-    if (t >= numTiles) { // device-side size is smaller than the host bound
-      __syncthreads();
-      continue;
-    }
+    if (blk < max(1u, nb)) { // else: the device-side size is smaller than the host bound
+      uint8_t* ans = (uint8_t*)el.out;
+      uint8_t* fbase = nullptr; // float archive (behind the sparse header + bitmap when nested)
+      if (a.floatType != kFtNone) {
+        fbase = (uint8_t*)el.out + el.sizeBias;
+        ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
+        if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
+      }
+      const uint32_t blkLen = blk < nb ? min(kBlockSyms, n - blk * kBlockSyms) : 0u;
+      const uint8_t* src =
+          (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + (size_t)blk * kBlockSyms;
+      const uint32_t numChunks = divUp(blkLen, kChunk);
+      const bool bulk = (((uintptr_t)src) & 15u) == 0;
 
-    // where this element's ANS archive lives
-    uint8_t* ans = (uint8_t*)el.out;
-    uint8_t* fbase = nullptr; // float archive (behind the sparse header + bitmap when nested)
-    if (a.floatType != kFtNone) {
-      fbase = (uint8_t*)el.out + el.sizeBias;
-      ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
-      if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
-    }
-
-    sTab[tid] = p.table[e * 256 + tid];
-
-    // ---- stage this tile's symbols in shared memory (any input alignment) ----
-    const uint8_t* elemStart = a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in;
-    const uint8_t* elemEnd = elemStart + n;
-    const uint32_t symOff = t * kTileSyms;
-    const uint32_t len = n > symOff ? min(kTileSyms, n - symOff) : 0;
-    const uint8_t* g = elemStart + symOff;
-    const uint32_t mis = (uint32_t)((uintptr_t)g & 15u);
-    {
-      const uint8_t* gA = g - mis;
-      const uint32_t nvec = len ? divUp(mis + len, 16) : 0;
-      for (uint32_t v = tid; v < nvec; v += kThreads) {
-        const uint8_t* src = gA + 16 * (size_t)v;
-        uint4 val;
-        if (src >= elemStart && src + 16 <= elemEnd) {
-          val = *(const uint4*)src;
-        } else {
-          uint32_t b[4] = {0, 0, 0, 0};
-#pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            const uint8_t* c = src + k;
-            if (c >= elemStart && c < elemEnd) b[k >> 2] |= (uint32_t)(*c) << (8 * (k & 3));
+      // ---- start pulling symbols: the first kRingSlots chunks ----
+      auto issueChunk = [&](uint32_t c) {
+        const uint32_t slot = c & (kRingSlots - 1);
+        const uint32_t len = min(kChunk, blkLen - c * kChunk);
+        if (bulk) {
+          if (lane == 0) {
+            const uint32_t bytes = roundUp(len, 16);
+            mbarExpectTx(bar0 + 8 * slot, bytes);
+            bulkLoad(ringAddr + slot * kChunk, src + c * kChunk, bytes, bar0 + 8 * slot);
           }
-          val = make_uint4(b[0], b[1], b[2], b[3]);
-        }
-        ((uint4*)sSym)[v] = val;
-      }
-    }
-    __syncthreads();
-
-    // ---- encode: warp w owns block t*8 + w ----
-    const uint32_t blk = t * kTileBlocks + w;
-    uint32_t blkLen = 0;
-    if (blk < nb) blkLen = min(kBlockSyms, n - blk * kBlockSyms);
-    uint16_t* stage = sStage + w * kStageWords;
-    uint32_t state = kStateMin, words = 0;
-    if (blkLen) {
-      const uint8_t* sym = sSym + mis + w * kBlockSyms + lane;
-      const uint32_t rows = blkLen >> 5;
-#pragma unroll 8
-      for (uint32_t r = 0; r < rows; ++r) encRow<PB>(state, sym[r * 32], sTab, stage, words, ltMask, true);
-      const uint32_t rem = blkLen & 31u;
-      if (rem) {
-        bool valid = lane < rem;
-        uint32_t sv = valid ? sym[rows * 32] : 0u;
-        encRow<PB>(state, sv, sTab, stage, words, ltMask, valid);
-      }
-      // zero the padding up to a multiple of 8 words (the reference leaves it undefined)
-      uint32_t padded = roundUp(words, 8);
-      if (words + lane < padded) stage[words + lane] = 0;
-    }
-    if (lane == 0) sWords[w] = roundUp(words, 8);
-    __syncthreads();
-
-    uint32_t myOff = 0, tileWords = 0;
+        } else { // unaligned input: plain loads (4-byte words when possible)
+          const uint8_t* g = src + c * kChunk + lane * 16;
+          uint8_t* d = ring + slot * kChunk + lane * 16;
+          if ((((uintptr_t)g) & 3u) == 0 && lane * 16 + 16 <= len) {
+            const uint32_t* g4 = (const uint32_t*)g;
+            *(uint4*)d = make_uint4(g4[0], g4[1], g4[2], g4[3]);
+          } else {
 #pragma unroll
-    for (uint32_t j = 0; j < kTileBlocks; ++j) {
-      uint32_t x = sWords[j];
-      myOff += j < w ? x : 0u;
-      tileWords += x;
-    }
-    if (w == 0) {
-      uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileWords, p.errFlag);
-      if (lane == 0) sExcl = ex;
-    }
-    __syncthreads();
-    const uint32_t excl = sExcl;
+            for (int k = 0; k < 16; ++k)
+              if (lane * 16 + k < len) d[k] = g[k];
+          }
+        }
+      };
+      for (uint32_t c = 0; c < min(numChunks, kRingSlots); ++c) issueChunk(c);
 
-    // ---- write this block: states, index entry, payload (dietgpu/ans/GpuANSEncode.cuh:584-623) ----
-    if (blkLen) {
-      const uint32_t startWord = excl + myOff;
-      ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
-      if (lane == 0) {
-        uint2* bw = (uint2*)(ans + kAnsFixedBytes + 128u * nb);
-        bw[blk] = make_uint2((blkLen << 16) | words, startWord);
+      // ---- the element's encode table ----
+      if (e != curElem) {
+        const uint4* t4 = (const uint4*)(p.table + (size_t)e * 256);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) ((uint4*)tab)[k * 32 + lane] = t4[k * 32 + lane];
+        curElem = e;
       }
       __syncwarp();
-      uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)startWord);
-      const uint4* src = (const uint4*)stage;
-      const uint32_t nv = roundUp(words, 8) >> 3;
-      for (uint32_t i = lane; i < nv; i += 32) dst[i] = src[i];
-    }
-    if (t == 0) { // pdf table (:568-573); zero for an empty element
-      uint32_t pdf = n ? (sTab[tid].y & 0xfffu) : 0u;
-      ((uint16_t*)(ans + kAnsHeaderBytes))[tid] = (uint16_t)pdf;
-    }
-    if (t == numTiles - 1 && tid == 0) {
-      const uint32_t totalWords = excl + tileWords;
-      uint32_t cs = (a.useChecksum && a.checksum) ? a.checksum[e] : 0u;
-      uint4* h = (uint4*)ans; // :533-565; fields the reference leaves undefined are written as 0
-      h[0] = make_uint4(kAnsMagic, nb, n, totalWords);
-      h[1] = make_uint4((uint32_t)PB | (a.useChecksum ? 16u : 0u), cs, 0u, 0u);
-      if (nb & 1u) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[nb] = make_uint2(0u, 0u);
-      const uint32_t total = ansOverhead(nb) + 2u * totalWords;
-      if (a.floatType != kFtNone && a.round == 0)
-        *(uint32_t*)(fbase + 16) = total; // GpuFloatHeader2.firstCompSegmentBytes
-      if (a.outSize) {
-        if (a.round) a.outSize[e] += total;
-        else
-          a.outSize[e] = el.sizeBias + total +
-                         (a.floatType != kFtNone ? kFloatHeaderBytes + floatRawBytes(a.floatType, n) : 0u);
+
+      // ---- encode ----
+      uint32_t state = kStateMin, outBytes = 0;
+      for (uint32_t c = 0; c < numChunks; ++c) {
+        const uint32_t slot = c & (kRingSlots - 1);
+        if (bulk) {
+          mbarWait(bar0 + 8 * slot, (phaseBits >> slot) & 1u);
+          phaseBits ^= 1u << slot;
+        } else {
+          __syncwarp();
+        }
+        const uint32_t symAddr = ringAddr + slot * kChunk + lane;
+        const uint32_t len = min(kChunk, blkLen - c * kChunk);
+        if (len == kChunk) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint2 ent[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+              uint32_t sym;
+              asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + (half * 8 + r) * 32));
+              asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent[r].x), "=r"(ent[r].y) : "r"(tabAddr + sym * 8));
+            }
+#pragma unroll
+            for (int r = 0; r < 8; ++r) encStep<PB>(state, ent[r], stageAddr, outBytes, ltMask);
+          }
+        } else {
+          const uint32_t rows = len >> 5, rem = len & 31u;
+          for (uint32_t r = 0; r < rows; ++r) {
+            uint32_t sym;
+            uint2 ent;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + r * 32));
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent.x), "=r"(ent.y) : "r"(tabAddr + sym * 8));
+            encStep<PB>(state, ent, stageAddr, outBytes, ltMask);
+          }
+          if (rem) {
+            const bool valid = lane < rem;
+            uint32_t sym = 0;
+            uint2 ent;
+            if (valid) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + rows * 32));
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent.x), "=r"(ent.y) : "r"(tabAddr + sym * 8));
+            encStepPartial<PB>(state, ent, stageAddr, outBytes, ltMask, valid);
+          }
+        }
+        // this slot is consumed: refill it with the chunk kRingSlots ahead
+        if (c + kRingSlots < numChunks) {
+          __syncwarp();
+          issueChunk(c + kRingSlots);
+        }
       }
+      const uint32_t words = outBytes >> 1;
+      const uint32_t padded = roundUp(words, 8);
+      // zero the padding up to a multiple of 8 words (the reference leaves it undefined)
+      if (words + lane < padded) ((uint16_t*)stage)[words + lane] = 0;
+      __syncwarp();
+
+      // ---- output offset of this block inside the element's payload ----
+      const uint32_t excl = lookbackExclusive(p.tileState + el.blockBase, blk, padded, p.errFlag);
+
+      // ---- write: states, index entry, payload (dietgpu/ans/GpuANSEncode.cuh:584-623) ----
+      if (blkLen) {
+        ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
+        if (lane == 0) {
+          uint2* bw = (uint2*)(ans + kAnsFixedBytes + 128u * nb);
+          bw[blk] = make_uint2((blkLen << 16) | words, excl);
+        }
+        uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)excl);
+        const uint4* st4 = (const uint4*)stage;
+        const uint32_t nv = padded >> 3;
+        for (uint32_t i = lane; i < nv; i += 32) dst[i] = st4[i];
+      }
+      if (blk == 0) { // pdf table (:568-573); zero for absent symbols and for an empty element
+        uint16_t* pdfOut = (uint16_t*)(ans + kAnsHeaderBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint2 en = tab[k * 32 + lane];
+          const uint32_t pdf = (n && en.x) ? (1u << PB) - (en.y & 0xfffu) : 0u;
+          pdfOut[k * 32 + lane] = (uint16_t)pdf;
+        }
+      }
+      if (blk == max(1u, nb) - 1 && lane == 0) {
+        const uint32_t totalWords = excl + padded;
+        uint32_t cs = (a.useChecksum && a.checksum) ? a.checksum[e] : 0u;
+        uint4* h = (uint4*)ans; // :533-565; fields the reference leaves undefined are written as 0
+        h[0] = make_uint4(kAnsMagic, nb, n, totalWords);
+        h[1] = make_uint4((uint32_t)PB | (a.useChecksum ? 16u : 0u), cs, 0u, 0u);
+        if (nb & 1u) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[nb] = make_uint2(0u, 0u);
+        const uint32_t total = ansOverhead(nb) + 2u * totalWords;
+        if (a.floatType != kFtNone && a.round == 0)
+          *(uint32_t*)(fbase + 16) = total; // GpuFloatHeader2.firstCompSegmentBytes
+        if (a.outSize) {
+          if (a.round) a.outSize[e] += total;
+          else
+            a.outSize[e] = el.sizeBias + total +
+                           (a.floatType != kFtNone ? kFloatHeaderBytes + floatRawBytes(a.floatType, n) : 0u);
+        }
+      }
+      __syncwarp();
     }
+    if (lane == 0) tkLane0 = atomicAdd(p.ticket, 1u);
+    tk = __shfl_sync(0xffffffffu, tkLane0, 0);
   }
 }
 
@@ -454,7 +545,7 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
   if (a.numElems == 0) return kOk;
   if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
   uint2* table = tmp.alloc<uint2>((size_t)a.numElems * 256);
-  // tile states + ticket + error flag share one zeroed region
+  // block states + ticket + error flag share one zeroed region
   size_t zeroBytes = (size_t)a.totalTiles * 8 + 16;
   uint8_t* zero = (uint8_t*)tmp.alloc(zeroBytes);
   if (tmp.failed()) return kErrCuda;
@@ -471,20 +562,20 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
   p.tileState = (unsigned long long*)zero;
   p.ticket = (uint32_t*)(zero + (size_t)a.totalTiles * 8);
   p.errFlag = p.ticket + 1;
-  uint32_t grid = min(a.totalTiles, (uint32_t)smCount() * 2u);
-  auto launch = [&](auto kern) -> int {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEncSmem));
+  uint32_t grid = min(divUp(a.totalTiles, kEncWarps), (uint32_t)smCount() * 6u);
+  auto launch = [&](auto kern, uint32_t smemBytes) -> int {
+    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     {
       ProfScope ps__("k_encode", s);
-      kern<<<grid, kThreads, kEncSmem, s>>>(p);
+      kern<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
     }
     DGB_CUDA(cudaGetLastError());
     return kOk;
   };
   switch (a.probBits) {
-    case 9: return launch(k_encode<9>);
-    case 10: return launch(k_encode<10>);
-    default: return launch(k_encode<11>);
+    case 9: return launch(k_encode<9>, kEncWarps * encWarpSmem<9>());
+    case 10: return launch(k_encode<10>, kEncWarps * encWarpSmem<10>());
+    default: return launch(k_encode<11>, kEncWarps * encWarpSmem<11>());
   }
 }
 

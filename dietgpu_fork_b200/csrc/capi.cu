@@ -27,6 +27,7 @@ bool validFloatType(int ft) { return ft >= kFtF16 && ft <= kFtF64; }
 struct WorkList {
   std::vector<Elem> elems; // numElems + 1 (sentinel)
   uint32_t totalTiles = 0;
+  uint32_t totalBlocks = 0; // 4096-unit blocks, at least one per element
   uint64_t planeUnits = 0; // sum of roundUp(n, 16)
   uint32_t maxN = 0;
 };
@@ -34,7 +35,7 @@ struct WorkList {
 int buildWorkList(WorkList& wl, uint32_t num, const void* const* in, void* const* out, const uint32_t* n,
                   uint32_t tileUnits) {
   wl.elems.resize((size_t)num + 1);
-  uint64_t tiles = 0, plane = 0;
+  uint64_t tiles = 0, plane = 0, blocks = 0;
   for (uint32_t i = 0; i < num; ++i) {
     Elem& e = wl.elems[i];
     e.in = in[i];
@@ -43,17 +44,21 @@ int buildWorkList(WorkList& wl, uint32_t num, const void* const* in, void* const
     e.tileBase = (uint32_t)tiles;
     e.planeOff = plane;
     e.sizeBias = 0;
-    e.pad = 0;
+    e.blockBase = (uint32_t)blocks;
     uint32_t t = divUp(n[i], tileUnits);
     tiles += t ? t : 1;
+    uint32_t b = divUp(n[i], kBlockSyms);
+    blocks += b ? b : 1;
     plane += roundUpSz(n[i], 16);
     if (n[i] > wl.maxN) wl.maxN = n[i];
-    if (tiles > 0x7fffffffull) return kErrInvalidArg;
+    if (tiles > 0x7fffffffull || blocks > 0x7fffffffull) return kErrInvalidArg;
   }
   Elem& s = wl.elems[num];
   memset(&s, 0, sizeof(Elem));
   s.tileBase = (uint32_t)tiles;
+  s.blockBase = (uint32_t)blocks;
   wl.totalTiles = (uint32_t)tiles;
+  wl.totalBlocks = (uint32_t)blocks;
   wl.planeUnits = plane;
   return kOk;
 }
@@ -142,7 +147,7 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   EncodeArgs a;
   a.elems = elemsDev;
   a.numElems = num;
-  a.totalTiles = wl.totalTiles;
+  a.totalTiles = wl.totalBlocks;
   a.nDev = nullptr;
   a.planeBase = nullptr;
   a.hist = hist;
@@ -216,7 +221,7 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     EncodeArgs a;
     a.elems = elemsDev;
     a.numElems = num;
-    a.totalTiles = wl.totalTiles;
+    a.totalTiles = wl.totalBlocks;
     a.nDev = nDev;
     a.planeBase = plane + planeBytes * r;
     a.hist = hist + (size_t)r * num * 256;

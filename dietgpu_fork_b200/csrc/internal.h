@@ -29,7 +29,7 @@ struct Elem {
   uint32_t tileBase; // first tile of this element in the call's work list
   uint64_t planeOff; // byte offset of this element's row in the exponent-plane temp (16-B aligned)
   uint32_t sizeBias; // added to the reported compressed size (sparse: header + bitmap bytes)
-  uint32_t pad;
+  uint32_t blockBase; // first 4096-symbol block of this element in the call's block list (encoder)
 };
 static_assert(sizeof(Elem) == 40 || sizeof(Elem) == 48, "Elem layout");
 
@@ -116,7 +116,7 @@ int smCount();
 struct EncodeArgs {
   const Elem* elems;        // device, numElems + 1
   uint32_t numElems;
-  uint32_t totalTiles;
+  uint32_t totalTiles;      // total 4096-symbol blocks (Elem::blockBase of the sentinel)
   const uint32_t* nDev;     // nullable: device-side symbol counts overriding Elem::n (sparse nnz)
   const uint8_t* planeBase; // nullable: symbols come from planeBase + Elem::planeOff instead of Elem::in
   const uint32_t* hist;     // device [numElems][256]
