@@ -21,7 +21,7 @@ struct DecParams {
   DecodeArgs a;
   const DecInfo* info;  // [planes][numElems]
   const uint32_t* lut;  // [planes][numElems][1 << probBits]
-  uint32_t* ticket;
+  uint32_t tilesPerCta; // every CTA owns a contiguous range of 8-block tiles
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -109,150 +109,254 @@ __global__ void __launch_bounds__(256) k_decodePrep(const DecodeArgs a, DecInfo*
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tile decoder
+// Block decoder: 8 warps per CTA share the element's LUT(s) in shared memory; apart from the
+// barrier pair at an element change the warps are autonomous, one ANS block each.
+//
+//   compressed words: the decoder walks a block's words from the end. They are pulled into a
+//       2 KB per-warp shared-memory ring in 1 KB pieces by cp.async.bulk (TMA 1-D) + mbarrier,
+//       always keeping the piece under the read pointer and the one below it resident, so the
+//       renormalisation read inside the dependent chain is an LDS.
+//   symbols: 16 rows (512 symbols) at a time into a double-buffered 512-byte transposer, then
+//       written out by the same warp with 16-byte vectors: plain bytes, or float words joined
+//       with the raw section (both planes first for fp64).
+// The small footprint (~3 KB per warp) is what buys occupancy: the per-row dependent chain holds
+// two LDS and a POPC, so throughput comes from many resident warps.
 // ---------------------------------------------------------------------------------------------
+constexpr uint32_t kDecWarps = 8;
+constexpr uint32_t kPieceWords = 512;                 // 1 KB
+constexpr uint32_t kDecRingBytes = 2 * kPieceWords * 2; // 2 pieces
+constexpr uint32_t kDecChunk = 512;                   // symbols per transposer buffer (16 rows)
+
+template <int PLANES> __host__ __device__ constexpr uint32_t decWarpSmem() {
+  return PLANES * (kDecRingBytes + 2 * kDecChunk + 16);
+}
+template <int PB, int PLANES> __host__ __device__ constexpr uint32_t decCtaSmem() {
+  return PLANES * (4u << PB) + kDecWarps * decWarpSmem<PLANES>();
+}
+
+// per-plane decode context of one warp
+struct DecCtx {
+  uint32_t state;
+  uint32_t ptrBytes;   // 2 * (index one past the next word to read)
+  int reqLo, readyLo;  // lowest piece requested / waited for
+  const uint8_t* src;  // this block's first payload word
+  uint32_t totalBytes; // roundUp(words, 8) * 2
+  uint32_t ringAddr, bar0, lutAddr;
+};
+
+__device__ __forceinline__ void decRequest(DecCtx& c, int upTo, uint32_t lane) {
+  // request pieces reqLo-1 ... upTo (descending); slot = piece & 1
+  while (c.reqLo > upTo) {
+    --c.reqLo;
+    if (lane == 0) {
+      const uint32_t off = (uint32_t)c.reqLo * kPieceWords * 2;
+      const uint32_t bytes = min(kPieceWords * 2, c.totalBytes - off);
+      const uint32_t slot = (uint32_t)c.reqLo & 1u;
+      mbarExpectTx(c.bar0 + 8 * slot, bytes);
+      bulkLoad(c.ringAddr + slot * kPieceWords * 2, c.src + off, bytes, c.bar0 + 8 * slot);
+    }
+  }
+}
+
 template <int PB>
-__device__ __forceinline__ uint32_t decRow(uint32_t& state, const uint32_t* __restrict__ lut,
-                                           const uint16_t* __restrict__ stage, uint32_t& ptr,
-                                           uint32_t geMask, bool valid) {
-  const uint32_t e = lut[state & ((1u << PB) - 1u)];
+__device__ __forceinline__ uint32_t decStep(uint32_t& state, const DecCtx& c, uint32_t& ptrBytes,
+                                            uint32_t geMask, bool valid) {
+  uint32_t e;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(c.lutAddr + ((state & ((1u << PB) - 1u)) << 2)));
   uint32_t ns = ((e >> 8) & 0xfffu) * (state >> PB) + (e >> 20);
-  state = valid ? ns : state;
-  const bool rd = valid && state < kStateMin;
+  ns = valid ? ns : state;
+  const bool rd = valid && ns < kStateMin;
   const uint32_t vote = __ballot_sync(0xffffffffu, rd);
-  if (rd) state = (state << 16) + stage[ptr - __popc(vote & geMask)];
-  ptr -= __popc(vote);
-  return e & 0xffu;
+  if (rd) {
+    uint32_t w;
+    const uint32_t a = c.ringAddr + ((ptrBytes - 2u * __popc(vote & geMask)) & (kDecRingBytes - 1));
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(w) : "r"(a));
+    ns = (ns << 16) | w;
+  }
+  state = ns;
+  ptrBytes -= 2u * __popc(vote);
+  return e;
 }
 
 template <int FT>
-__device__ __forceinline__ void writeTile(const DecInfo& d, const Elem& el, const DecodeArgs& a, uint32_t t,
-                                          const uint8_t* sSym0, const uint8_t* sSym1, uint32_t tid) {
-  const uint32_t off = t * kTileSyms;
-  const uint32_t len = min(kTileSyms, d.n - off);
+__device__ __forceinline__ void writeChunk(const DecInfo& d, uint8_t* outBase, uint32_t wordOff, uint32_t len,
+                                           const uint8_t* sym0, const uint8_t* sym1, uint32_t lane) {
   if constexpr (FT == kFtNone) {
-    uint8_t* out = (uint8_t*)el.out + off;
-    if ((((uintptr_t)out) & 15u) == 0) {
-      const uint32_t nv = len >> 4;
-      for (uint32_t i = tid; i < nv; i += kThreads) ((uint4*)out)[i] = ((const uint4*)sSym0)[i];
-      const uint32_t done = nv << 4;
-      if (tid < len - done) out[done + tid] = sSym0[done + tid];
+    uint8_t* out = outBase + wordOff;
+    if ((((uintptr_t)out) & 15u) == 0 && len == kDecChunk) {
+      ((uint4*)out)[lane] = ((const uint4*)sym0)[lane];
     } else {
-      for (uint32_t i = tid; i < len; i += kThreads) out[i] = sSym0[i];
+      for (uint32_t i = lane; i < len; i += 32) out[i] = sym0[i];
     }
   } else {
-    using Tr = FloatTraits<FT>;
-    constexpr uint32_t G = Tr::kGroup;
-    uint8_t* outBase = a.denseBase ? a.denseBase + el.planeOff * sizeof(typename Tr::Word) : (uint8_t*)el.out;
-    RawSections rs = rawSections(FT, (uint8_t*)d.fbase + kFloatHeaderBytes, d.n);
+    constexpr uint32_t G = FloatTraits<FT>::kGroup;
+    const RawSections rs = rawSections(FT, (uint8_t*)d.fbase + kFloatHeaderBytes, d.n);
     uint32_t vecWords = 0;
     if ((((uintptr_t)outBase) & 15u) == 0) {
-      const uint32_t ng = len / G;
-      const uint32_t g0 = off / G;
+      const uint32_t ng = len / G, g0 = wordOff / G;
       uint4* o = (uint4*)outBase;
-      for (uint32_t i = tid; i < ng; i += kThreads)
-        o[g0 + i] = joinGroup<FT>(g0 + i, sSym0 + i * G, sSym1 + i * G, rs);
+#pragma unroll 2
+      for (uint32_t i = lane; i < ng; i += 32) o[g0 + i] = joinGroup<FT>(g0 + i, sym0 + i * G, sym1 + i * G, rs);
       vecWords = ng * G;
     }
-    for (uint32_t i = vecWords + tid; i < len; i += kThreads)
-      joinScalar<FT>(outBase, off + i, sSym0[i], sSym1[i], rs);
+    for (uint32_t i = vecWords + lane; i < len; i += 32)
+      joinScalar<FT>(outBase, wordOff + i, sym0[i], sym1[i], rs);
   }
 }
 
 template <int PB, int FT>
-__global__ void __launch_bounds__(256, FT == kFtF64 ? 1 : 2) k_decode(const DecParams p) {
+__global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode(const DecParams p) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t kLut = 1u << PB;
-  extern __shared__ __align__(16) uint8_t smem[];
-  uint8_t* sSym = smem;                                                 // kPlanes * kTileSyms
-  uint16_t* sStage = (uint16_t*)(smem + kPlanes * kTileSyms);          // 8 * kStageWords
-  uint32_t* sLut = (uint32_t*)(smem + kPlanes * kTileSyms + kTileBlocks * kStageWords * 2);
-  __shared__ uint32_t sTicket, sElem;
-
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint32_t* sLut = (uint32_t*)smem; // kPlanes * kLut
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  uint8_t* ws = smem + kPlanes * kLut * 4 + w * decWarpSmem<kPlanes>();
+  // per plane: ring | transposer[2] | 2 mbarriers
+  uint8_t* trans[kPlanes];
+  DecCtx ctx[kPlanes];
+#pragma unroll
+  for (int pl = 0; pl < kPlanes; ++pl) {
+    uint8_t* base = ws + pl * (kDecRingBytes + 2 * kDecChunk + 16);
+    ctx[pl].ringAddr = smemAddr(base);
+    trans[pl] = base + kDecRingBytes;
+    ctx[pl].bar0 = smemAddr(base + kDecRingBytes + 2 * kDecChunk);
+    ctx[pl].lutAddr = smemAddr(sLut + pl * kLut);
+    if (lane == 0) {
+      mbarInit(ctx[pl].bar0, 1);
+      mbarInit(ctx[pl].bar0 + 8, 1);
+    }
+  }
+  if (lane == 0) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncwarp();
+  uint32_t phaseBits = 0; // bit (2 * plane + slot)
   const uint32_t geMask = laneMaskGe();
   const DecodeArgs& a = p.a;
-  uint32_t guess = 0;
 
-  while (true) {
-    if (tid == 0) {
-      uint32_t tk = atomicAdd(p.ticket, 1u);
-      sTicket = tk;
-      if (tk < a.totalTiles) sElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tk, guess);
-    }
-    __syncthreads();
-    const uint32_t tk = sTicket;
-    if (tk >= a.totalTiles) break;
-    const uint32_t e = sElem;
-    guess = e;
-    const Elem el = a.elems[e];
-    const uint32_t t = tk - el.tileBase;
-    const DecInfo d0 = p.info[e];
-    if (!d0.ok || t >= divUp(d0.nb, kTileBlocks)) {
+  const uint32_t t0 = blockIdx.x * p.tilesPerCta;
+  const uint32_t t1 = min(t0 + p.tilesPerCta, a.totalTiles);
+  uint32_t cur = 0xffffffffu;
+  for (uint32_t tile = t0; tile < t1; ++tile) {
+    const uint32_t e = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, cur);
+    if (e != cur) { // CTA-uniform: every warp of the CTA walks the same tile sequence
       __syncthreads();
-      continue;
-    }
-    const uint32_t nb = d0.nb;
-    const uint32_t blk = t * kTileBlocks + w;
-
+      if (p.info[e].ok && p.info[e].n) {
 #pragma unroll
-    for (int plane = 0; plane < kPlanes; ++plane) {
-      const uint8_t* ans = plane == 0 ? d0.ans : p.info[a.numElems + e].ans;
-      {
-        const uint4* src = (const uint4*)(p.lut + ((size_t)plane * a.numElems + e) * kLut);
-        for (uint32_t i = tid; i < kLut / 4; i += kThreads) ((uint4*)sLut)[i] = src[i];
-      }
-      uint32_t state = 0, len = 0, words = 0;
-      uint16_t* stage = sStage + w * kStageWords;
-      if (blk < nb) {
-        state = ((const uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane];
-        const uint2 bw = ((const uint2*)(ans + kAnsFixedBytes + 128u * nb))[blk];
-        len = min(bw.x >> 16, kBlockSyms);
-        words = min(bw.x & 0xffffu, kStageWords);
-        const uint4* src = (const uint4*)(ans + ansOverhead(nb) + 2 * (size_t)bw.y);
-        const uint32_t nv = roundUp(words, 8) >> 3;
-        for (uint32_t i = lane; i < nv; i += 32) ((uint4*)stage)[i] = src[i];
+        for (int pl = 0; pl < kPlanes; ++pl) {
+          const uint4* src = (const uint4*)(p.lut + ((size_t)pl * a.numElems + e) * kLut);
+          for (uint32_t i = tid; i < kLut / 4; i += kDecWarps * 32) ((uint4*)(sLut + pl * kLut))[i] = src[i];
+        }
       }
       __syncthreads();
-      if (len) {
-        uint8_t* sym = sSym + plane * kTileSyms + w * kBlockSyms + lane;
-        const uint32_t rows = len >> 5, rem = len & 31u;
-        uint32_t ptr = words;
+      cur = e;
+    }
+    const DecInfo d0 = p.info[e];
+    const Elem el = a.elems[e];
+    const uint32_t blk = (tile - el.tileBase) * kTileBlocks + w;
+    if (!d0.ok || blk >= d0.nb) continue;
+    const uint32_t nb = d0.nb;
+
+    uint32_t blkLen = 0;
+#pragma unroll
+    for (int pl = 0; pl < kPlanes; ++pl) {
+      const uint8_t* ans = pl == 0 ? d0.ans : p.info[a.numElems + e].ans;
+      DecCtx& c = ctx[pl];
+      c.state = ((const uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane];
+      const uint2 bw = ((const uint2*)(ans + kAnsFixedBytes + 128u * nb))[blk];
+      blkLen = min(bw.x >> 16, kBlockSyms);
+      const uint32_t words = min(bw.x & 0xffffu, kStageWords);
+      c.src = ans + ansOverhead(nb) + 2 * (size_t)bw.y;
+      c.totalBytes = roundUp(words, 8) * 2;
+      c.ptrBytes = words * 2;
+      const int top = words ? (int)((words - 1) / kPieceWords) : -1;
+      c.reqLo = c.readyLo = top + 1;
+      __syncwarp(); // every lane is done with the ring of the previous block
+      decRequest(c, max(top - 1, 0), lane);
+    }
+    uint8_t* outBase;
+    if constexpr (FT == kFtNone) outBase = (uint8_t*)el.out + (size_t)blk * kBlockSyms;
+    else
+      outBase = a.denseBase ? a.denseBase + el.planeOff * sizeof(typename FloatTraits<FT == kFtNone ? kFtF16 : FT>::Word)
+                            : (uint8_t*)el.out;
+
+    const uint32_t numChunks = divUp(blkLen, kDecChunk);
+    for (int c = (int)numChunks - 1; c >= 0; --c) {
+      const uint32_t len = min(kDecChunk, blkLen - (uint32_t)c * kDecChunk);
+      const uint32_t rows = len >> 5, rem = len & 31u;
+      const uint32_t buf = (uint32_t)c & 1u;
+#pragma unroll
+      for (int pl = 0; pl < kPlanes; ++pl) {
+        DecCtx& cx = ctx[pl];
+        // the piece under the read pointer and the one below must have landed
+        const int q = cx.ptrBytes ? (int)((cx.ptrBytes / 2 - 1) / kPieceWords) : -1;
+        const int need = q >= 0 ? max(q - 1, 0) : 0x7fffffff;
+        while (cx.readyLo > need) {
+          --cx.readyLo;
+          const uint32_t slot = (uint32_t)cx.readyLo & 1u;
+          mbarWait(cx.bar0 + 8 * slot, (phaseBits >> (2 * pl + slot)) & 1u);
+          phaseBits ^= 1u << (2 * pl + slot);
+        }
+        uint32_t state = cx.state, ptrBytes = cx.ptrBytes;
+        const uint32_t symAddr = smemAddr(trans[pl] + buf * kDecChunk) + lane;
         if (rem) {
           const bool valid = lane < rem;
-          uint32_t sv = decRow<PB>(state, sLut, stage, ptr, geMask, valid);
-          if (valid) sym[rows * 32] = (uint8_t)sv;
+          const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, valid);
+          if (valid) asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + rows * 32), "r"(ev) : "memory");
         }
-#pragma unroll 8
-        for (int r = (int)rows - 1; r >= 0; --r) sym[r * 32] = (uint8_t)decRow<PB>(state, sLut, stage, ptr, geMask, true);
+        if (rows == 16) {
+#pragma unroll
+          for (int r = 15; r >= 0; --r) {
+            const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, true);
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + r * 32), "r"(ev) : "memory");
+          }
+        } else {
+          for (int r = (int)rows - 1; r >= 0; --r) {
+            const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, true);
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + r * 32), "r"(ev) : "memory");
+          }
+        }
+        cx.state = state;
+        cx.ptrBytes = ptrBytes;
+        // keep the piece under the new read pointer and the one below it in flight
+        const int nq = ptrBytes ? (int)((ptrBytes / 2 - 1) / kPieceWords) : -1;
+        if (nq >= 1 && cx.reqLo > nq - 1) {
+          __syncwarp(); // all lanes are past their reads of the slot being refilled
+          decRequest(cx, nq - 1, lane);
+        }
       }
-      __syncthreads();
+      __syncwarp();
+      const uint32_t wordOff = FT == kFtNone ? (uint32_t)c * kDecChunk : blk * kBlockSyms + (uint32_t)c * kDecChunk;
+      writeChunk<FT>(d0, outBase, wordOff, len, trans[0] + buf * kDecChunk, trans[kPlanes - 1] + buf * kDecChunk,
+                     lane);
     }
-    writeTile<FT>(d0, el, a, t, sSym, sSym + (kPlanes - 1) * kTileSyms, tid);
   }
 }
 
 template <int PB, int FT>
-static int launchDecodeKernel(const DecParams& p, uint32_t grid, cudaStream_t s) {
+static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
-  constexpr uint32_t smemBytes = kPlanes * kTileSyms + kTileBlocks * kStageWords * 2 + (4u << PB);
+  constexpr uint32_t smemBytes = decCtaSmem<PB, kPlanes>();
   DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  const uint32_t perSm = FT == kFtF64 ? 3u : 6u;
+  uint32_t ctas = min(p.a.totalTiles, (uint32_t)smCount() * perSm);
+  p.tilesPerCta = divUp(p.a.totalTiles, ctas);
+  ctas = divUp(p.a.totalTiles, p.tilesPerCta);
   {
     ProfScope ps__("k_decode", s);
-    k_decode<PB, FT><<<grid, kThreads, smemBytes, s>>>(p);
+    k_decode<PB, FT><<<ctas, kDecWarps * 32, smemBytes, s>>>(p);
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;
 }
 
 template <int PB>
-static int launchDecodeFt(const DecParams& p, uint32_t grid, cudaStream_t s) {
+static int launchDecodeFt(DecParams& p, cudaStream_t s) {
   switch (p.a.floatType) {
-    case kFtNone: return launchDecodeKernel<PB, kFtNone>(p, grid, s);
-    case kFtF16: return launchDecodeKernel<PB, kFtF16>(p, grid, s);
-    case kFtBF16: return launchDecodeKernel<PB, kFtBF16>(p, grid, s);
-    case kFtF32: return launchDecodeKernel<PB, kFtF32>(p, grid, s);
-    case kFtF64: return launchDecodeKernel<PB, kFtF64>(p, grid, s);
+    case kFtNone: return launchDecodeKernel<PB, kFtNone>(p, s);
+    case kFtF16: return launchDecodeKernel<PB, kFtF16>(p, s);
+    case kFtBF16: return launchDecodeKernel<PB, kFtBF16>(p, s);
+    case kFtF32: return launchDecodeKernel<PB, kFtF32>(p, s);
+    case kFtF64: return launchDecodeKernel<PB, kFtF64>(p, s);
     default: return kErrInvalidArg;
   }
 }
@@ -263,9 +367,7 @@ int launchDecode(Temp& tmp, const DecodeArgs& a, cudaStream_t s) {
   const int planes = a.floatType == kFtF64 ? 2 : 1;
   DecInfo* info = tmp.alloc<DecInfo>((size_t)planes * a.numElems);
   uint32_t* lut = tmp.alloc<uint32_t>(((size_t)planes * a.numElems) << a.probBits);
-  uint32_t* ticket = tmp.alloc<uint32_t>(4);
   if (tmp.failed()) return kErrCuda;
-  DGB_CUDA(cudaMemsetAsync(ticket, 0, 16, s));
   {
     ProfScope ps__("k_decodePrep", s);
     k_decodePrep<<<dim3(a.numElems, planes), 256, 0, s>>>(a, info, lut);
@@ -275,14 +377,12 @@ int launchDecode(Temp& tmp, const DecodeArgs& a, cudaStream_t s) {
   p.a = a;
   p.info = info;
   p.lut = lut;
-  p.ticket = ticket;
-  uint32_t perSm = a.floatType == kFtF64 ? 1u : 2u;
-  uint32_t grid = min(a.totalTiles, (uint32_t)smCount() * perSm);
-  if (grid == 0) return kOk;
+  p.tilesPerCta = 1;
+  if (a.totalTiles == 0) return kOk;
   switch (a.probBits) {
-    case 9: return launchDecodeFt<9>(p, grid, s);
-    case 10: return launchDecodeFt<10>(p, grid, s);
-    default: return launchDecodeFt<11>(p, grid, s);
+    case 9: return launchDecodeFt<9>(p, s);
+    case 10: return launchDecodeFt<10>(p, s);
+    default: return launchDecodeFt<11>(p, s);
   }
 }
 

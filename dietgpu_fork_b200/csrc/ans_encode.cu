@@ -294,33 +294,6 @@ constexpr uint32_t kChunk = 512; // symbols per ring slot = 16 rows
 template <int PB> __host__ __device__ constexpr uint32_t stageBytes() { return PB <= 10 ? 5120u : 5632u; }
 template <int PB> __host__ __device__ constexpr uint32_t encWarpSmem() { return kRingSlots * kChunk + stageBytes<PB>() + 2048u + 64u; }
 
-__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbarExpectTx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra WAIT_DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "WAIT_DONE:\n"
-      "}\n" ::"r"(bar), "r"(parity)
-      : "memory");
-}
-// global -> shared bulk copy (16-byte aligned source, destination and size), completion on `bar`
-__device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-
 // One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90), table entry already in registers.
 template <int PB>
 __device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t stageAddr, uint32_t& outBytes,
