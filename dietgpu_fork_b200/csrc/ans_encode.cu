@@ -270,72 +270,106 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 }
 
 // ---------------------------------------------------------------------------------------------
-// Block encoder: one autonomous warp per 4096-symbol ANS block, no CTA-wide barrier anywhere.
+// Block encoder + compaction (two kernels).
 //
-//   ticket (atomicAdd, prefetched one block ahead) -> (element, block)
+// k_encode: one autonomous warp per 4096-symbol ANS block, no CTA-wide barrier, no waiting on
+// other warps.
 //   symbols: 512-byte chunks (16 symbol rows) pulled into a 4-deep per-warp shared-memory ring by
 //            cp.async.bulk (TMA 1-D) + mbarrier, issued 4 chunks ahead of their use
-//   table:   the element's 2 KB encode table, copied into the warp's shared memory when it changes
-//   rows:    rANS step per 32 symbols, ballot/popc compaction into a per-warp staging buffer
-//   offset:  decoupled look-back over the element's per-block aggregates (roundUp(words, 8))
-//   output:  states, index entry and payload written once, at their final place
+//   table:   the element's 2 KB encode table, read through L1
+//   rows:    rANS step per 32 symbols, ballot/popc compaction into a 1 KB per-warp staging buffer
+//   flush:   after every chunk the staged words go, as 16-byte vectors, to the block's slot of a
+//            scratch area; final lane states go straight into the archive, the word count into
+//            a per-block size array
+// k_coalesce: per tile of 8 blocks, a warp-shuffle / decoupled look-back exclusive scan of the
+// per-block sizes (roundUp(words, 8)) gives every block its final offset; the payload is copied
+// from the scratch slots (L2-resident: just written) to its final place together with the block
+// index, the pdf table and the header.
+//
+// Why not a single pass: a block's final offset is known only when ALL earlier blocks of the
+// element are encoded, i.e. after the slowest of them; measured on B200, warps spent as long
+// waiting on that look-back as encoding (profiles/r1_k_encode_v2), and holding a worst-case 5 KB
+// block in shared memory while waiting capped occupancy at 24 warps/SM.
 // ---------------------------------------------------------------------------------------------
 struct EncParams {
   EncodeArgs a;
-  const uint2* table;            // [numElems][256]
-  unsigned long long* tileState; // [totalBlocks], zeroed
+  const uint2* table;   // [numElems][256]
+  uint8_t* scratch;     // [totalBlocks][kSlotBytes]
+  uint32_t* blockWords; // [totalBlocks] words emitted per block
+  uint32_t totalWarps;
+  // k_coalesce only
+  uint32_t totalTiles;           // 8-block tiles (Elem::tileBase units)
+  unsigned long long* tileState; // [totalTiles], zeroed
   uint32_t* ticket;              // zeroed
   uint32_t* errFlag;
 };
 
 constexpr uint32_t kEncWarps = 4;
 constexpr uint32_t kRingSlots = 4;
-constexpr uint32_t kChunk = 512; // symbols per ring slot = 16 rows
-template <int PB> __host__ __device__ constexpr uint32_t stageBytes() { return PB <= 10 ? 5120u : 5632u; }
-template <int PB> __host__ __device__ constexpr uint32_t encWarpSmem() { return kRingSlots * kChunk + stageBytes<PB>() + 2048u + 64u; }
+constexpr uint32_t kChunk = 512;                 // symbols per ring slot = 16 rows
+constexpr uint32_t kEncStageBytes = 1024 + 32;   // 16 rows x 64 B + carry
+constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
+constexpr uint32_t kEncWarpSmem = kRingSlots * kChunk + kEncStageBytes + 32;
 
-// One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90), table entry already in registers.
+// One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
+// {magic, (K - pdf) | shift << 12 | cdf << 17}; outPtr = shared-memory byte address of the next
+// free staging word. Written in PTX to pin the instruction selection (~19 instructions).
 template <int PB>
-__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t stageAddr, uint32_t& outBytes,
-                                        uint32_t ltMask) {
-  const bool wr = (int32_t)((e.y << (31 - PB)) + state) < 0; // state >= pdf << (31 - PB)
-  const uint32_t vote = __ballot_sync(0xffffffffu, wr);
-  if (wr) {
-    uint32_t addr = stageAddr + outBytes + 2u * __popc(vote & ltMask);
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)state) : "memory");
-    state >>= 16;
-  }
-  outBytes += 2u * __popc(vote);
-  const uint32_t q = __funnelshift_r(__umulhi(state, e.x) + state, 0u, e.y >> 12);
-  state = q * (e.y & 0xfffu) + state + (e.y >> 17);
+__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b32 sum, vote, pre, addr, t, q, c, k;\n"
+      "mad.lo.u32 sum, %3, %5, %0;\n"          // ((K - pdf) << (31 - PB)) + state: bit 31 <=> renormalise
+      "setp.lt.s32 p, sum, 0;\n"
+      "vote.sync.ballot.b32 vote, p, 0xffffffff;\n"
+      "and.b32 pre, vote, %4;\n"
+      "popc.b32 pre, pre;\n"
+      "mad.lo.u32 addr, pre, 2, %1;\n"
+      "@p st.shared.u16 [addr], %0;\n"
+      "@p shr.u32 %0, %0, 16;\n"
+      "popc.b32 t, vote;\n"
+      "mad.lo.u32 %1, t, 2, %1;\n"
+      "mul.hi.u32 t, %0, %2;\n"
+      "add.u32 t, t, %0;\n"
+      "shr.u32 c, %3, 12;\n"
+      "shf.r.wrap.b32 q, t, 0, c;\n"           // floor(state / pdf)
+      "and.b32 k, %3, 0xfff;\n"
+      "shr.u32 c, %3, 17;\n"
+      "add.u32 c, c, %0;\n"                    // state + cdf
+      "mad.lo.u32 %0, q, k, c;\n"              // q * (K - pdf) + state + cdf
+      "}\n"
+      : "+r"(state), "+r"(outPtr)
+      : "r"(e.x), "r"(e.y), "r"(ltMask), "n"(1u << (31 - PB))
+      : "memory");
 }
 
+// partial last row: lanes >= rem neither emit nor update (:94-136)
 template <int PB>
-__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t stageAddr, uint32_t& outBytes,
-                                               uint32_t ltMask, bool valid) {
+__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask,
+                                               bool valid) {
   const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
   const uint32_t vote = __ballot_sync(0xffffffffu, wr);
   if (wr) {
-    uint32_t addr = stageAddr + outBytes + 2u * __popc(vote & ltMask);
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)state) : "memory");
+    uint32_t addr = outPtr + 2u * __popc(vote & ltMask);
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "r"(state) : "memory");
     state >>= 16;
   }
-  outBytes += 2u * __popc(vote);
+  outPtr += 2u * __popc(vote);
   const uint32_t q = __funnelshift_r(__umulhi(state, e.x) + state, 0u, e.y >> 12);
   const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
   state = valid ? ns : state;
 }
 
 template <int PB>
-__global__ void __launch_bounds__(kEncWarps * 32, 6) k_encode(const EncParams p) {
+__global__ void __launch_bounds__(kEncWarps * 32, 10) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  uint8_t* ws = smem + w * encWarpSmem<PB>();
-  uint8_t* ring = ws;                                         // kRingSlots * kChunk
-  uint8_t* stage = ws + kRingSlots * kChunk;                  // stageBytes
-  uint2* tab = (uint2*)(stage + stageBytes<PB>());            // 256 entries
-  const uint32_t bar0 = smemAddr(tab + 256);                  // kRingSlots mbarriers
-  const uint32_t ringAddr = smemAddr(ring), stageAddr = smemAddr(stage), tabAddr = smemAddr(tab);
+  uint8_t* ws = smem + w * kEncWarpSmem;
+  uint8_t* ring = ws;                        // kRingSlots * kChunk
+  uint8_t* stage = ws + kRingSlots * kChunk; // kEncStageBytes
+  const uint32_t bar0 = smemAddr(stage + kEncStageBytes); // kRingSlots mbarriers
+  const uint32_t ringAddr = smemAddr(ring), stageAddr = smemAddr(stage);
   const uint32_t ltMask = laneMaskLt();
   const EncodeArgs& a = p.a;
 
@@ -346,180 +380,225 @@ __global__ void __launch_bounds__(kEncWarps * 32, 6) k_encode(const EncParams p)
   }
   __syncwarp();
   uint32_t phaseBits = 0; // parity expected at the next wait on each slot
+  uint32_t guess = 0;
 
-  // Tickets are taken only when the warp is ready to start the block: a ticket reserved ahead of
-  // time would be a block that later tickets wait on (look-back) while nobody works on it.
-  uint32_t tkLane0 = 0;
-  if (lane == 0) tkLane0 = atomicAdd(p.ticket, 1u);
-  uint32_t tk = __shfl_sync(0xffffffffu, tkLane0, 0);
-  uint32_t curElem = 0xffffffffu, guess = 0;
-
-  while (tk < a.totalTiles) {
-
-    const uint32_t e = findElement(&a.elems[0].blockBase, sizeof(Elem) / 4, a.numElems, tk, guess);
+  // blocks are independent here: static striding, consecutive warps take consecutive blocks
+  for (uint32_t gb = blockIdx.x * kEncWarps + w; gb < a.totalTiles; gb += p.totalWarps) {
+    const uint32_t e = findElement(&a.elems[0].blockBase, sizeof(Elem) / 4, a.numElems, gb, guess);
     guess = e;
     const Elem el = a.elems[e];
-    const uint32_t blk = tk - el.blockBase;
+    const uint32_t blk = gb - el.blockBase;
     const uint32_t n = a.nDev ? a.nDev[e] : el.n;
     const uint32_t nb = divUp(n, kBlockSyms);
-    if (blk < max(1u, nb)) { // else: the device-side size is smaller than the host bound
-      uint8_t* ans = (uint8_t*)el.out;
-      uint8_t* fbase = nullptr; // float archive (behind the sparse header + bitmap when nested)
-      if (a.floatType != kFtNone) {
-        fbase = (uint8_t*)el.out + el.sizeBias;
-        ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
-        if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
-      }
-      const uint32_t blkLen = blk < nb ? min(kBlockSyms, n - blk * kBlockSyms) : 0u;
-      const uint8_t* src =
-          (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + (size_t)blk * kBlockSyms;
-      const uint32_t numChunks = divUp(blkLen, kChunk);
-      const bool bulk = (((uintptr_t)src) & 15u) == 0;
-
-      // ---- start pulling symbols: the first kRingSlots chunks ----
-      auto issueChunk = [&](uint32_t c) {
-        const uint32_t slot = c & (kRingSlots - 1);
-        const uint32_t len = min(kChunk, blkLen - c * kChunk);
-        if (bulk) {
-          if (lane == 0) {
-            const uint32_t bytes = roundUp(len, 16);
-            mbarExpectTx(bar0 + 8 * slot, bytes);
-            bulkLoad(ringAddr + slot * kChunk, src + c * kChunk, bytes, bar0 + 8 * slot);
-          }
-        } else { // unaligned input: plain loads (4-byte words when possible)
-          const uint8_t* g = src + c * kChunk + lane * 16;
-          uint8_t* d = ring + slot * kChunk + lane * 16;
-          if ((((uintptr_t)g) & 3u) == 0 && lane * 16 + 16 <= len) {
-            const uint32_t* g4 = (const uint32_t*)g;
-            *(uint4*)d = make_uint4(g4[0], g4[1], g4[2], g4[3]);
-          } else {
-#pragma unroll
-            for (int k = 0; k < 16; ++k)
-              if (lane * 16 + k < len) d[k] = g[k];
-          }
-        }
-      };
-      for (uint32_t c = 0; c < min(numChunks, kRingSlots); ++c) issueChunk(c);
-
-      // ---- the element's encode table ----
-      if (e != curElem) {
-        const uint4* t4 = (const uint4*)(p.table + (size_t)e * 256);
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < 4; ++k) ((uint4*)tab)[k * 32 + lane] = t4[k * 32 + lane];
-        curElem = e;
-      }
-      __syncwarp();
-
-      // ---- encode ----
-      uint32_t state = kStateMin, outBytes = 0;
-      for (uint32_t c = 0; c < numChunks; ++c) {
-        const uint32_t slot = c & (kRingSlots - 1);
-        if (bulk) {
-          mbarWait(bar0 + 8 * slot, (phaseBits >> slot) & 1u);
-          phaseBits ^= 1u << slot;
-        } else {
-          __syncwarp();
-        }
-        const uint32_t symAddr = ringAddr + slot * kChunk + lane;
-        const uint32_t len = min(kChunk, blkLen - c * kChunk);
-        if (len == kChunk) {
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint2 ent[8];
-#pragma unroll
-            for (int r = 0; r < 8; ++r) {
-              uint32_t sym;
-              asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + (half * 8 + r) * 32));
-              asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent[r].x), "=r"(ent[r].y) : "r"(tabAddr + sym * 8));
-            }
-#pragma unroll
-            for (int r = 0; r < 8; ++r) encStep<PB>(state, ent[r], stageAddr, outBytes, ltMask);
-          }
-        } else {
-          const uint32_t rows = len >> 5, rem = len & 31u;
-          for (uint32_t r = 0; r < rows; ++r) {
-            uint32_t sym;
-            uint2 ent;
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + r * 32));
-            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent.x), "=r"(ent.y) : "r"(tabAddr + sym * 8));
-            encStep<PB>(state, ent, stageAddr, outBytes, ltMask);
-          }
-          if (rem) {
-            const bool valid = lane < rem;
-            uint32_t sym = 0;
-            uint2 ent;
-            if (valid) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + rows * 32));
-            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ent.x), "=r"(ent.y) : "r"(tabAddr + sym * 8));
-            encStepPartial<PB>(state, ent, stageAddr, outBytes, ltMask, valid);
-          }
-        }
-        // this slot is consumed: refill it with the chunk kRingSlots ahead
-        if (c + kRingSlots < numChunks) {
-          __syncwarp();
-          issueChunk(c + kRingSlots);
-        }
-      }
-      const uint32_t words = outBytes >> 1;
-      const uint32_t padded = roundUp(words, 8);
-      // zero the padding up to a multiple of 8 words (the reference leaves it undefined)
-      if (words + lane < padded) ((uint16_t*)stage)[words + lane] = 0;
-      __syncwarp();
-
-      // ---- output offset of this block inside the element's payload ----
-      const uint32_t excl = lookbackExclusive(p.tileState + el.blockBase, blk, padded, p.errFlag);
-
-      // ---- write: states, index entry, payload (dietgpu/ans/GpuANSEncode.cuh:584-623) ----
-      if (blkLen) {
-        ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
-        if (lane == 0) {
-          uint2* bw = (uint2*)(ans + kAnsFixedBytes + 128u * nb);
-          bw[blk] = make_uint2((blkLen << 16) | words, excl);
-        }
-        uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)excl);
-        const uint4* st4 = (const uint4*)stage;
-        const uint32_t nv = padded >> 3;
-        for (uint32_t i = lane; i < nv; i += 32) dst[i] = st4[i];
-      }
-      if (blk == 0) { // pdf table (:568-573); zero for absent symbols and for an empty element
-        uint16_t* pdfOut = (uint16_t*)(ans + kAnsHeaderBytes);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint2 en = tab[k * 32 + lane];
-          const uint32_t pdf = (n && en.x) ? (1u << PB) - (en.y & 0xfffu) : 0u;
-          pdfOut[k * 32 + lane] = (uint16_t)pdf;
-        }
-      }
-      if (blk == max(1u, nb) - 1 && lane == 0) {
-        const uint32_t totalWords = excl + padded;
-        uint32_t cs = (a.useChecksum && a.checksum) ? a.checksum[e] : 0u;
-        uint4* h = (uint4*)ans; // :533-565; fields the reference leaves undefined are written as 0
-        h[0] = make_uint4(kAnsMagic, nb, n, totalWords);
-        h[1] = make_uint4((uint32_t)PB | (a.useChecksum ? 16u : 0u), cs, 0u, 0u);
-        if (nb & 1u) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[nb] = make_uint2(0u, 0u);
-        const uint32_t total = ansOverhead(nb) + 2u * totalWords;
-        if (a.floatType != kFtNone && a.round == 0)
-          *(uint32_t*)(fbase + 16) = total; // GpuFloatHeader2.firstCompSegmentBytes
-        if (a.outSize) {
-          if (a.round) a.outSize[e] += total;
-          else
-            a.outSize[e] = el.sizeBias + total +
-                           (a.floatType != kFtNone ? kFloatHeaderBytes + floatRawBytes(a.floatType, n) : 0u);
-        }
-      }
-      __syncwarp();
+    if (blk >= nb) { // empty element, or the device-side size is smaller than the host bound
+      if (lane == 0) p.blockWords[gb] = 0;
+      continue;
     }
-    if (lane == 0) tkLane0 = atomicAdd(p.ticket, 1u);
-    tk = __shfl_sync(0xffffffffu, tkLane0, 0);
+    uint8_t* ans = (uint8_t*)el.out;
+    if (a.floatType != kFtNone) {
+      const uint8_t* fbase = (const uint8_t*)el.out + el.sizeBias;
+      ans = (uint8_t*)fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
+      if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
+    }
+    const uint32_t blkLen = min(kBlockSyms, n - blk * kBlockSyms);
+    const uint8_t* src =
+        (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + (size_t)blk * kBlockSyms;
+    const uint32_t numChunks = divUp(blkLen, kChunk);
+    const bool bulk = (((uintptr_t)src) & 15u) == 0;
+    uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
+    const uint2* __restrict__ tab = p.table + (size_t)e * 256;
+
+    auto issueChunk = [&](uint32_t c) {
+      const uint32_t sl = c & (kRingSlots - 1);
+      const uint32_t len = min(kChunk, blkLen - c * kChunk);
+      if (bulk) {
+        if (lane == 0) {
+          const uint32_t bytes = roundUp(len, 16);
+          mbarExpectTx(bar0 + 8 * sl, bytes);
+          bulkLoad(ringAddr + sl * kChunk, src + c * kChunk, bytes, bar0 + 8 * sl);
+        }
+      } else { // unaligned input: plain loads (4-byte words when possible)
+        const uint8_t* g = src + c * kChunk + lane * 16;
+        uint8_t* d = ring + sl * kChunk + lane * 16;
+        if ((((uintptr_t)g) & 3u) == 0 && lane * 16 + 16 <= len) {
+          const uint32_t* g4 = (const uint32_t*)g;
+          *(uint4*)d = make_uint4(g4[0], g4[1], g4[2], g4[3]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (lane * 16 + k < len) d[k] = g[k];
+        }
+      }
+    };
+    __syncwarp();
+    for (uint32_t c = 0; c < min(numChunks, kRingSlots); ++c) issueChunk(c);
+
+    uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
+    for (uint32_t c = 0; c < numChunks; ++c) {
+      const uint32_t sl = c & (kRingSlots - 1);
+      if (bulk) {
+        mbarWait(bar0 + 8 * sl, (phaseBits >> sl) & 1u);
+        phaseBits ^= 1u << sl;
+      } else {
+        __syncwarp();
+      }
+      const uint32_t symAddr = ringAddr + sl * kChunk + lane;
+      const uint32_t len = min(kChunk, blkLen - c * kChunk);
+      if (len == kChunk) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint2 ent[8];
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            uint32_t sym;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + (half * 8 + r) * 32));
+            ent[r] = __ldg(tab + sym);
+          }
+#pragma unroll
+          for (int r = 0; r < 8; ++r) encStep<PB>(state, ent[r], outPtr, ltMask);
+        }
+      } else {
+        const uint32_t rows = len >> 5, rem = len & 31u;
+        for (uint32_t r = 0; r < rows; ++r) {
+          uint32_t sym;
+          asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + r * 32));
+          encStep<PB>(state, __ldg(tab + sym), outPtr, ltMask);
+        }
+        if (rem) {
+          const bool valid = lane < rem;
+          uint32_t sym = 0;
+          if (valid) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + rows * 32));
+          encStepPartial<PB>(state, __ldg(tab + sym), outPtr, ltMask, valid);
+        }
+      }
+      __syncwarp();
+      // this ring slot is consumed: refill it with the chunk kRingSlots ahead
+      if (c + kRingSlots < numChunks) issueChunk(c + kRingSlots);
+      // flush the staged words: whole 16-byte vectors go to the scratch slot, the rest is carried
+      uint32_t bytes = outPtr - stageAddr;
+      if (c + 1 == numChunks) { // last chunk: pad with zero words to a multiple of 8 words
+        const uint32_t padded = roundUp(bytes, 16);
+        if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
+        __syncwarp();
+        if (lane == 0) p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
+        bytes = padded;
+      }
+      const uint32_t nv = bytes >> 4;
+      for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
+      const uint32_t remBytes = bytes & 15u;
+      uint32_t carry = 0;
+      if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
+      __syncwarp();
+      if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
+      __syncwarp();
+      flushedVecs += nv;
+      outPtr = stageAddr + remBytes;
+    }
+    // final lane states go straight to their place in the archive (:584-589)
+    ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
   }
 }
 
-int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
+// Compaction: tile = 8 consecutive blocks of one element, one warp per block.
+__global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBits) {
+  __shared__ uint32_t sTicket, sElem, sExcl;
+  __shared__ uint32_t sWords[kTileBlocks];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const EncodeArgs& a = p.a;
+  uint32_t guess = 0;
+  while (true) {
+    if (tid == 0) {
+      uint32_t tk = atomicAdd(p.ticket, 1u);
+      sTicket = tk;
+      if (tk < p.totalTiles) sElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tk, guess);
+    }
+    __syncthreads();
+    const uint32_t tk = sTicket;
+    if (tk >= p.totalTiles) break;
+    const uint32_t e = sElem;
+    guess = e;
+    const Elem el = a.elems[e];
+    const uint32_t t = tk - el.tileBase;
+    const uint32_t n = a.nDev ? a.nDev[e] : el.n;
+    const uint32_t nb = divUp(n, kBlockSyms);
+    const uint32_t numTiles = max(1u, divUp(nb, kTileBlocks));
+    if (t >= numTiles) { // device-side size is smaller than the host bound
+      __syncthreads();
+      continue;
+    }
+    uint8_t* ans = (uint8_t*)el.out;
+    uint8_t* fbase = nullptr;
+    if (a.floatType != kFtNone) {
+      fbase = (uint8_t*)el.out + el.sizeBias;
+      ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
+      if (a.round) ans += *(const uint32_t*)(fbase + 16);
+    }
+    const uint32_t blk = t * kTileBlocks + w;
+    const uint32_t gb = el.blockBase + blk;
+    uint32_t blkLen = 0, words = 0;
+    if (blk < nb) {
+      blkLen = min(kBlockSyms, n - blk * kBlockSyms);
+      words = p.blockWords[gb];
+    }
+    if (lane == 0) sWords[w] = roundUp(words, 8);
+    __syncthreads();
+    uint32_t myOff = 0, tileWords = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < kTileBlocks; ++j) {
+      uint32_t x = sWords[j];
+      myOff += j < w ? x : 0u;
+      tileWords += x;
+    }
+    if (w == 0) {
+      uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileWords, p.errFlag);
+      if (lane == 0) sExcl = ex;
+    }
+    __syncthreads();
+    const uint32_t excl = sExcl;
+    if (blkLen) { // index entry and payload (dietgpu/ans/GpuANSEncode.cuh:591-623)
+      const uint32_t startWord = excl + myOff;
+      if (lane == 0) {
+        uint2* bw = (uint2*)(ans + kAnsFixedBytes + 128u * nb);
+        bw[blk] = make_uint2((blkLen << 16) | words, startWord);
+      }
+      uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)startWord);
+      const uint4* src = (const uint4*)(p.scratch + (size_t)gb * kSlotBytes);
+      const uint32_t nv = roundUp(words, 8) >> 3;
+      for (uint32_t i = lane; i < nv; i += 32) dst[i] = src[i];
+    }
+    if (t == 0) { // pdf table (:568-573); zero for absent symbols and for an empty element
+      const uint2 en = p.table[(size_t)e * 256 + tid];
+      const uint32_t pdf = (n && en.x) ? (1u << probBits) - (en.y & 0xfffu) : 0u;
+      ((uint16_t*)(ans + kAnsHeaderBytes))[tid] = (uint16_t)pdf;
+    }
+    if (t == numTiles - 1 && tid == 0) {
+      const uint32_t totalWords = excl + tileWords;
+      uint32_t cs = (a.useChecksum && a.checksum) ? a.checksum[e] : 0u;
+      uint4* h = (uint4*)ans; // :533-565; fields the reference leaves undefined are written as 0
+      h[0] = make_uint4(kAnsMagic, nb, n, totalWords);
+      h[1] = make_uint4((uint32_t)probBits | (a.useChecksum ? 16u : 0u), cs, 0u, 0u);
+      if (nb & 1u) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[nb] = make_uint2(0u, 0u);
+      const uint32_t total = ansOverhead(nb) + 2u * totalWords;
+      if (a.floatType != kFtNone && a.round == 0)
+        *(uint32_t*)(fbase + 16) = total; // GpuFloatHeader2.firstCompSegmentBytes
+      if (a.outSize) {
+        if (a.round) a.outSize[e] += total;
+        else
+          a.outSize[e] = el.sizeBias + total +
+                         (a.floatType != kFtNone ? kFloatHeaderBytes + floatRawBytes(a.floatType, n) : 0u);
+      }
+    }
+  }
+}
+
+int launchAnsEncode(Temp& tmp, const EncodeArgs& a, uint32_t totalTiles, cudaStream_t s) {
   if (a.numElems == 0) return kOk;
   if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
   uint2* table = tmp.alloc<uint2>((size_t)a.numElems * 256);
-  // block states + ticket + error flag share one zeroed region
-  size_t zeroBytes = (size_t)a.totalTiles * 8 + 16;
+  uint32_t* blockWords = tmp.alloc<uint32_t>(a.totalTiles);
+  uint8_t* scratch = (uint8_t*)tmp.alloc((size_t)a.totalTiles * kSlotBytes);
+  // tile states + ticket + error flag share one zeroed region
+  size_t zeroBytes = (size_t)totalTiles * 8 + 16;
   uint8_t* zero = (uint8_t*)tmp.alloc(zeroBytes);
   if (tmp.failed()) return kErrCuda;
   DGB_CUDA(cudaMemsetAsync(zero, 0, zeroBytes, s));
@@ -532,12 +611,16 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
   EncParams p;
   p.a = a;
   p.table = table;
+  p.scratch = scratch;
+  p.blockWords = blockWords;
+  p.totalTiles = totalTiles;
   p.tileState = (unsigned long long*)zero;
-  p.ticket = (uint32_t*)(zero + (size_t)a.totalTiles * 8);
+  p.ticket = (uint32_t*)(zero + (size_t)totalTiles * 8);
   p.errFlag = p.ticket + 1;
-  uint32_t grid = min(divUp(a.totalTiles, kEncWarps), (uint32_t)smCount() * 6u);
-  auto launch = [&](auto kern, uint32_t smemBytes) -> int {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  uint32_t grid = min(divUp(a.totalTiles, kEncWarps), (uint32_t)smCount() * 10u);
+  p.totalWarps = grid * kEncWarps;
+  const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
+  auto launch = [&](auto kern) -> int {
     {
       ProfScope ps__("k_encode", s);
       kern<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
@@ -545,11 +628,19 @@ int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s) {
     DGB_CUDA(cudaGetLastError());
     return kOk;
   };
+  int rc;
   switch (a.probBits) {
-    case 9: return launch(k_encode<9>, kEncWarps * encWarpSmem<9>());
-    case 10: return launch(k_encode<10>, kEncWarps * encWarpSmem<10>());
-    default: return launch(k_encode<11>, kEncWarps * encWarpSmem<11>());
+    case 9: rc = launch(k_encode<9>); break;
+    case 10: rc = launch(k_encode<10>); break;
+    default: rc = launch(k_encode<11>); break;
   }
+  if (rc) return rc;
+  {
+    ProfScope ps__("k_coalesce", s);
+    k_coalesce<<<min(totalTiles, (uint32_t)smCount() * 8u), 256, 0, s>>>(p, a.probBits);
+  }
+  DGB_CUDA(cudaGetLastError());
+  return kOk;
 }
 
 } // namespace dgb

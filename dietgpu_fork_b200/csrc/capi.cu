@@ -157,7 +157,7 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   a.round = 0;
   a.probBits = pb;
   a.useChecksum = useChecksum ? 1 : 0;
-  return launchAnsEncode(tmp, a, s);
+  return launchAnsEncode(tmp, a, wl.totalTiles, s);
 }
 
 int ansDecode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t num, const void* const* in,
@@ -231,7 +231,7 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     a.round = r;
     a.probBits = pb;
     a.useChecksum = 0; // not allowed in float mode (dietgpu/float/GpuFloatCodec.h:52)
-    if ((rc = launchAnsEncode(tmp, a, s))) return rc;
+    if ((rc = launchAnsEncode(tmp, a, wl.totalTiles, s))) return rc;
   }
   return kOk;
 }
@@ -445,7 +445,8 @@ size_t dgb_temp_bytes_required(int op, int ft, uint32_t num, uint32_t maxSize) {
   const size_t tiles = B * (divUp(maxSize, kTileSyms) + 1);
   const size_t spTiles = B * (divUp(maxSize, 8192) + 1);
   const size_t desc = (B + 1) * sizeof(Elem) + 512;
-  const size_t enc = B * 256 * 8 + tiles * 8 + 1024;           // tables + tile states
+  const size_t blocks = B * (divUp(maxSize, kBlockSyms) + 1);
+  const size_t enc = B * 256 * 8 + tiles * 8 + blocks * (4 + 5632) + 2048; // tables, tile states, scratch slots
   const size_t dec = B * (sizeof(DecInfo) + (4u << 11)) * 2 + 1024;
   const size_t row = roundUpSz(maxSize, 16);
   const size_t wb = floatWordBytes(ft);

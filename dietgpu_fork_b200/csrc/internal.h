@@ -128,7 +128,8 @@ struct EncodeArgs {
   int useChecksum;          // ANS-level checksum flag stored in the ANS header
 };
 // Enqueues normalise + encode for one exponent plane / byte stream. Scratch comes from `tmp`.
-int launchAnsEncode(Temp& tmp, const EncodeArgs& a, cudaStream_t s);
+// totalTiles = number of 8-block tiles of the work list (compaction kernel).
+int launchAnsEncode(Temp& tmp, const EncodeArgs& a, uint32_t totalTiles, cudaStream_t s);
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or
 // output (useOut = 1); n = nDev[e] when given, else Elem::n. maxUnits bounds n.
