@@ -4,6 +4,7 @@
 // caller's stream. Mirrors the host wrappers of the reference (dietgpu/ans/GpuANSEncode.cu:27-179,
 // dietgpu/ans/GpuANSDecode.cu:19-193, dietgpu/float/GpuFloatCompress.cu:50-162,
 // dietgpu/float/GpuFloatDecompress.cu:22-179, dietgpu/float/GpuSparseFloat{Compress,Decompress}.cu).
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -28,6 +29,7 @@ struct WorkList {
   std::vector<Elem> elems; // numElems + 1 (sentinel)
   uint32_t totalTiles = 0;
   uint32_t totalBlocks = 0; // 4096-unit blocks, at least one per element
+  uint32_t totalGroups = 0; // 256-block size groups, at least one per element
   uint64_t planeUnits = 0; // sum of roundUp(n, 16)
   uint32_t maxN = 0;
 };
@@ -35,7 +37,7 @@ struct WorkList {
 int buildWorkList(WorkList& wl, uint32_t num, const void* const* in, void* const* out, const uint32_t* n,
                   uint32_t tileUnits) {
   wl.elems.resize((size_t)num + 1);
-  uint64_t tiles = 0, plane = 0, blocks = 0;
+  uint64_t tiles = 0, plane = 0, blocks = 0, groups = 0;
   for (uint32_t i = 0; i < num; ++i) {
     Elem& e = wl.elems[i];
     e.in = in[i];
@@ -45,10 +47,13 @@ int buildWorkList(WorkList& wl, uint32_t num, const void* const* in, void* const
     e.planeOff = plane;
     e.sizeBias = 0;
     e.blockBase = (uint32_t)blocks;
+    e.groupBase = (uint32_t)groups;
+    e.pad = 0;
     uint32_t t = divUp(n[i], tileUnits);
     tiles += t ? t : 1;
     uint32_t b = divUp(n[i], kBlockSyms);
     blocks += b ? b : 1;
+    groups += divUp(b ? b : 1, 256);
     plane += roundUpSz(n[i], 16);
     if (n[i] > wl.maxN) wl.maxN = n[i];
     if (tiles > 0x7fffffffull || blocks > 0x7fffffffull) return kErrInvalidArg;
@@ -59,8 +64,14 @@ int buildWorkList(WorkList& wl, uint32_t num, const void* const* in, void* const
   s.blockBase = (uint32_t)blocks;
   wl.totalTiles = (uint32_t)tiles;
   wl.totalBlocks = (uint32_t)blocks;
+  wl.totalGroups = (uint32_t)groups;
+  s.groupBase = (uint32_t)groups;
   wl.planeUnits = plane;
   return kOk;
+}
+
+WorkRange wholeRange(const WorkList& wl, uint32_t num) {
+  return WorkRange{0, num, 0, wl.totalTiles, 0, wl.totalBlocks};
 }
 
 int upload(Temp& tmp, const WorkList& wl, Elem** dev, cudaStream_t s) {
@@ -157,7 +168,9 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   a.round = 0;
   a.probBits = pb;
   a.useChecksum = useChecksum ? 1 : 0;
-  return launchAnsEncode(tmp, a, wl.totalTiles, s);
+  EncodeScratch es;
+  if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es, s))) return rc;
+  return launchAnsEncode(a, es, wholeRange(wl, num), s);
 }
 
 int ansDecode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t num, const void* const* in,
@@ -197,6 +210,32 @@ int ansDecode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
 // ---- float ---------------------------------------------------------------------------------
 // Shared by floatCompress and the sparse path (which feeds the dense non-zeros with device-side
 // counts). wl.elems: in/out/n/tileBase/planeOff/sizeBias filled; elemsDev already uploaded.
+// Second stream (highest priority) on which the split kernels of the later element groups run
+// while the caller's stream encodes the earlier ones.
+cudaStream_t sideStream() {
+  static thread_local cudaStream_t side[16] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 16) return nullptr;
+  if (!side[dev]) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (cudaStreamCreateWithPriority(&side[dev], cudaStreamNonBlocking, hi) != cudaSuccess) side[dev] = nullptr;
+  }
+  return side[dev];
+}
+
+int overlapGroups() {
+  static int g = -1;
+  if (g < 0) {
+    const char* e = getenv("DGB_OVERLAP_GROUPS");
+    g = e ? atoi(e) : 1; // measured on B200: 2/4/8 groups are 1-19 % slower than 1 (kernels of two streams do not co-run well)
+    if (g < 1) g = 1;
+    if (g > 16) g = 16;
+  }
+  return g;
+}
+
 int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList& wl, uint32_t num,
                       const Elem* elemsDev, const uint32_t* nDev, const uint8_t* denseIn,
                       uint32_t* outSizeDev, cudaStream_t s) {
@@ -214,11 +253,10 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     if (denseIn) return kErrInvalidArg; // sparse + checksum: not supported (reference: untested)
     if ((rc = launchChecksum(elemsDev, num, wl.maxN, 1, nDev, 0, checksum, s))) return rc;
   }
-  if ((rc = launchFloatSplit(ft, elemsDev, num, wl.totalTiles, nDev, denseIn, plane, plane + planeBytes,
-                             hist, hist + (size_t)num * 256, checksum, useChecksum, s)))
-    return rc;
+  EncodeArgs args[2];
+  EncodeScratch es[2];
   for (int r = 0; r < planes; ++r) {
-    EncodeArgs a;
+    EncodeArgs& a = args[r];
     a.elems = elemsDev;
     a.numElems = num;
     a.totalTiles = wl.totalBlocks;
@@ -231,7 +269,53 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     a.round = r;
     a.probBits = pb;
     a.useChecksum = 0; // not allowed in float mode (dietgpu/float/GpuFloatCodec.h:52)
-    if ((rc = launchAnsEncode(tmp, a, wl.totalTiles, s))) return rc;
+    if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es[r], s))) return rc;
+  }
+
+  // Split is HBM-bound, the encoder issue-bound: cut the batch into element groups and run
+  // split(g + 1) on a side stream while the caller's stream encodes group g.
+  int groups = overlapGroups();
+  cudaStream_t side = nullptr;
+  if (num < 8 || wl.totalTiles < 1024 || planes > 1) groups = 1;
+  if (groups > 1) side = sideStream();
+  if (!side) groups = 1;
+  std::vector<WorkRange> ranges;
+  {
+    uint32_t e0 = 0;
+    for (int g = 0; g < groups; ++g) {
+      const uint32_t target = (uint32_t)(((uint64_t)wl.totalTiles * (g + 1)) / groups);
+      uint32_t e1 = e0;
+      while (e1 < num && (g == groups - 1 || wl.elems[e1 + 1].tileBase <= target)) ++e1;
+      if (g == groups - 1) e1 = num;
+      WorkRange r{e0, e1, wl.elems[e0].tileBase, wl.elems[e1].tileBase, wl.elems[e0].blockBase,
+                  wl.elems[e1].blockBase};
+      if (e1 > e0) ranges.push_back(r);
+      e0 = e1;
+    }
+  }
+  auto split = [&](const WorkRange& r, cudaStream_t st) {
+    return launchFloatSplit(ft, elemsDev, num, r.tile0, r.tile1, nDev, denseIn, plane, plane + planeBytes, hist,
+                            hist + (size_t)num * 256, checksum, useChecksum, st);
+  };
+  if (ranges.size() <= 1) {
+    const WorkRange all = wholeRange(wl, num);
+    if ((rc = split(all, s))) return rc;
+    for (int r = 0; r < planes; ++r)
+      if ((rc = launchAnsEncode(args[r], es[r], all, s))) return rc;
+    return kOk;
+  }
+  cudaEvent_t ev;
+  DGB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  DGB_CUDA(cudaEventRecord(ev, s));
+  DGB_CUDA(cudaStreamWaitEvent(side, ev, 0));
+  DGB_CUDA(cudaEventDestroy(ev));
+  for (size_t g = 0; g < ranges.size(); ++g) {
+    if ((rc = split(ranges[g], side))) return rc;
+    DGB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    DGB_CUDA(cudaEventRecord(ev, side));
+    DGB_CUDA(cudaStreamWaitEvent(s, ev, 0));
+    DGB_CUDA(cudaEventDestroy(ev));
+    if ((rc = launchAnsEncode(args[0], es[0], ranges[g], s))) return rc;
   }
   return kOk;
 }

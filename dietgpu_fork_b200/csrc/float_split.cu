@@ -18,7 +18,7 @@ constexpr uint32_t kSplitHistWords = 8 * 256 * kSplitRep; // per plane
 struct SplitParams {
   const Elem* elems;
   uint32_t numElems;
-  uint32_t totalTiles;
+  uint32_t tileBegin, tileEnd; // range of 32768-word tiles handled by this launch
   uint32_t tilesPerCta;
   const uint32_t* nDev;     // nullable (sparse: nnz)
   const uint8_t* denseIn;   // nullable: input rows at denseIn + planeOff * wordBytes (sparse)
@@ -62,8 +62,8 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
   uint32_t* wh1 = wh0 + kSplitHistWords;
   const uint32_t rep = tid & (kSplitRep - 1);
 
-  const uint32_t t0 = blockIdx.x * p.tilesPerCta;
-  const uint32_t t1 = min(t0 + p.tilesPerCta, p.totalTiles);
+  const uint32_t t0 = p.tileBegin + blockIdx.x * p.tilesPerCta;
+  const uint32_t t1 = min(t0 + p.tilesPerCta, p.tileEnd);
   uint32_t cur = 0xffffffffu;
   for (uint32_t tile = t0; tile < t1; ++tile) {
     const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tile, cur);
@@ -179,9 +179,10 @@ template <int FT>
 static int launchSplitT(SplitParams& p, cudaStream_t s) {
   constexpr uint32_t smemBytes = FloatTraits<FT>::kPlanes * kSplitHistWords * 4;
   DGB_CUDA(cudaFuncSetAttribute(k_floatSplit<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-  uint32_t ctas = min(p.totalTiles, (uint32_t)smCount() * (FT == kFtF64 ? 3u : 6u));
-  p.tilesPerCta = divUp(p.totalTiles, ctas);
-  ctas = divUp(p.totalTiles, p.tilesPerCta);
+  const uint32_t tiles = p.tileEnd - p.tileBegin;
+  uint32_t ctas = min(tiles, (uint32_t)smCount() * (FT == kFtF64 ? 3u : 6u));
+  p.tilesPerCta = divUp(tiles, ctas);
+  ctas = divUp(tiles, p.tilesPerCta);
   {
     ProfScope ps__("k_floatSplit", s);
     k_floatSplit<FT><<<ctas, 256, smemBytes, s>>>(p);
@@ -190,14 +191,16 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
   return kOk;
 }
 
-int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t totalTiles, const uint32_t* nDev,
+int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tileBegin, uint32_t tileEnd,
+                     const uint32_t* nDev,
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s) {
-  if (!totalTiles) return kOk;
+  if (tileEnd <= tileBegin) return kOk;
   SplitParams p;
   p.elems = elems;
   p.numElems = numElems;
-  p.totalTiles = totalTiles;
+  p.tileBegin = tileBegin;
+  p.tileEnd = tileEnd;
   p.tilesPerCta = 1;
   p.nDev = nDev;
   p.denseIn = denseIn;

@@ -30,8 +30,10 @@ struct Elem {
   uint64_t planeOff; // byte offset of this element's row in the exponent-plane temp (16-B aligned)
   uint32_t sizeBias; // added to the reported compressed size (sparse: header + bitmap bytes)
   uint32_t blockBase; // first 4096-symbol block of this element in the call's block list (encoder)
+  uint32_t groupBase; // first 256-block size group of this element (compaction)
+  uint32_t pad;
 };
-static_assert(sizeof(Elem) == 40 || sizeof(Elem) == 48, "Elem layout");
+static_assert(sizeof(Elem) == 48, "Elem layout");
 
 // Per (element, plane) decode descriptor produced on the device by k_decodePrep.
 struct DecInfo {
@@ -128,15 +130,29 @@ struct EncodeArgs {
   int useChecksum;          // ANS-level checksum flag stored in the ANS header
 };
 // Enqueues normalise + encode for one exponent plane / byte stream. Scratch comes from `tmp`.
-// totalTiles = number of 8-block tiles of the work list (compaction kernel).
-int launchAnsEncode(Temp& tmp, const EncodeArgs& a, uint32_t totalTiles, cudaStream_t s);
+// A slice of the work list: elements [e0, e1) with their 8-block tiles and 4096-symbol blocks.
+struct WorkRange {
+  uint32_t e0, e1, tile0, tile1, blk0, blk1;
+};
+// Scratch of one encode pass (one exponent plane / byte stream) over the whole work list.
+struct EncodeScratch {
+  uint2* table;
+  uint32_t* blockWords;
+  uint32_t* groupWords;
+  uint8_t* scratch;
+};
+// totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
+int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s);
+// Enqueues normalise + encode + compaction for the elements of `r` on stream s.
+int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or
 // output (useOut = 1); n = nDev[e] when given, else Elem::n. maxUnits bounds n.
 int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint32_t bytesPerUnit,
                    const uint32_t* nDev, int useOut, uint32_t* checksum, cudaStream_t s);
 
-int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t totalTiles, const uint32_t* nDev,
+int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tileBegin, uint32_t tileEnd,
+                     const uint32_t* nDev,
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s);
 
