@@ -290,3 +290,48 @@ def decompress_data_sparse(ts_in, ts_out, temp_mem=None, out_status=None, out_de
 OPS = ["max_float_compressed_output_size", "max_float_compressed_size", "max_any_compressed_output_size",
        "max_any_compressed_size", "compress_data", "compress_data_split_size", "compress_data_simple",
        "decompress_data", "decompress_data_split_size", "decompress_data_simple"]
+
+# ---- torch.ops.dietgpu.* registration --------------------------------------------------------------
+# Operator schemas, verbatim in meaning from the reference's TORCH_LIBRARY_FRAGMENT
+# (/root/reference/dietgpu/DietGpu.cpp:921-943), so that `torch.ops.dietgpu.compress_data(...)` call sites
+# (ans_test.py, float_test.py, benchmark.py) resolve to this library.
+_SCHEMAS = [
+    "max_float_compressed_output_size(Tensor[] ts) -> (int, int)",
+    "max_float_compressed_size(Tensor dtype, int size) -> int",
+    "max_any_compressed_output_size(Tensor[] ts) -> (int, int)",
+    "max_any_compressed_size(int bytes) -> int",
+    "compress_data(bool compress_as_float, Tensor[] ts_in, bool checksum=False, Tensor? temp_mem=None, "
+    "Tensor? out_compressed=None, Tensor? out_compressed_bytes=None) -> (Tensor, Tensor, int)",
+    "compress_data_split_size(bool compress_as_float, Tensor t_in, Tensor t_in_split_sizes, bool checksum=False, "
+    "Tensor? temp_mem=None, Tensor? out_compressed=None, Tensor? out_compressed_bytes=None) -> (Tensor[], Tensor, int)",
+    "compress_data_simple(bool compress_as_float, Tensor[] ts_in, bool checksum=False, int? temp_mem=67108864) "
+    "-> Tensor[]",
+    "decompress_data(bool compress_as_float, Tensor[] ts_in, Tensor[] ts_out, bool checksum=False, "
+    "Tensor? temp_mem=None, Tensor? out_status=None, Tensor? out_decompressed_words=None) -> (int)",
+    "decompress_data_split_size(bool compress_as_float, Tensor[] ts_in, Tensor t_out, Tensor t_out_split_sizes, "
+    "bool checksum=False, Tensor? temp_mem=None, Tensor? out_status=None, Tensor? out_decompressed_words=None) "
+    "-> (int)",
+    "decompress_data_simple(bool compress_as_float, Tensor[] ts_in, bool checksum=False, int? temp_mem=67108864) "
+    "-> Tensor[]",
+    # additions (the fork's sparse codec; no Python surface in the reference)
+    "max_sparse_float_compressed_size(Tensor dtype, int size) -> int",
+    "compress_data_sparse(Tensor[] ts_in, Tensor? temp_mem=None, Tensor? out_compressed=None, "
+    "Tensor? out_compressed_bytes=None) -> (Tensor, Tensor, int)",
+    "decompress_data_sparse(Tensor[] ts_in, Tensor[] ts_out, Tensor? temp_mem=None, Tensor? out_status=None, "
+    "Tensor? out_decompressed_words=None) -> (int)",
+]
+_lib = None
+
+
+def install():
+    """Register the operators under the `dietgpu` namespace (idempotent). Returns torch.ops.dietgpu."""
+    global _lib
+    if _lib is None:
+        lib = torch.library.Library("dietgpu", "DEF")
+        g = globals()
+        for schema in _SCHEMAS:
+            name = schema.split("(", 1)[0]
+            lib.define(schema)
+            lib.impl(name, g[name], "CompositeImplicitAutograd")
+        _lib = lib
+    return torch.ops.dietgpu

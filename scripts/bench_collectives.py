@@ -1,0 +1,87 @@
+"""BASELINE config 5: compressed all-gather / all-to-all of bf16 gradient shards vs the uncompressed NCCL
+collectives on the same box. Launch: python -m torch.distributed.run --nnodes=1 --nproc-per-node N
+--master-addr 127.0.0.1 --master-port P scripts/bench_collectives.py [--mib 64] [--steps 10] [--chunks 4].
+Effective GB/s = uncompressed bytes delivered per rank / time (CUDA events, max over ranks). Checks bit
+equality of the compressed result against the uncompressed collective's before timing."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dietgpu_fork_b200 import dist as dgd  # noqa: E402
+
+
+def timed(fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda")
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return ms.item()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mib", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--chunks", type=int, default=4)
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    n = a.mib * (1 << 20) // 2
+    g = torch.Generator(device="cuda").manual_seed(5000 + rank)
+    shard = (torch.randn(n, device="cuda", generator=g) * 0.02).to(torch.bfloat16)
+    temp = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    codec = dgd.CudaFloatCodec(temp_mem=temp)
+
+    # --- all-gather ---
+    raw = torch.empty((world, n), dtype=torch.bfloat16, device="cuda")
+    out = torch.empty_like(raw)
+    dist.all_gather_into_tensor(raw.view(-1), shard)
+    dgd.all_gather_compressed(shard, out=out, num_chunks=a.chunks, codec=codec)
+    assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "compressed all-gather is not bit exact"
+    t_raw = timed(lambda: dist.all_gather_into_tensor(raw.view(-1), shard), a.steps, a.warmup)
+    t_cmp = timed(lambda: dgd.all_gather_compressed(shard, out=out, num_chunks=a.chunks, codec=codec), a.steps,
+                  a.warmup)
+    delivered = world * n * 2
+    res = {"collective": "all_gather", "n_gpus": world, "shard_mib": a.mib, "chunks": a.chunks,
+           "nccl_raw_ms": t_raw, "compressed_ms": t_cmp,
+           "nccl_raw_gbs": delivered / t_raw / 1e6, "compressed_effective_gbs": delivered / t_cmp / 1e6}
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+
+    # --- all-to-all: mib/world MiB to every peer ---
+    per = n // world
+    send = shard[:per * world].view(world, per)
+    raw2 = torch.empty_like(send)
+    out2 = torch.empty_like(send)
+    dist.all_to_all_single(raw2.view(-1), send.reshape(-1))
+    dgd.all_to_all_compressed(send, out=out2, codec=codec)
+    assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "compressed all-to-all is not bit exact"
+    t_raw = timed(lambda: dist.all_to_all_single(raw2.view(-1), send.reshape(-1)), a.steps, a.warmup)
+    t_cmp = timed(lambda: dgd.all_to_all_compressed(send, out=out2, codec=codec), a.steps, a.warmup)
+    delivered = world * per * 2
+    res = {"collective": "all_to_all", "n_gpus": world, "chunk_mib": per * 2 / (1 << 20),
+           "nccl_raw_ms": t_raw, "compressed_ms": t_cmp,
+           "nccl_raw_gbs": delivered / t_raw / 1e6, "compressed_effective_gbs": delivered / t_cmp / 1e6}
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
