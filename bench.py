@@ -305,8 +305,13 @@ def main():
     alg = {  # algorithmic bytes per launch on this workload (DESIGN.md "Kernels")
         "k_floatSplit": U + N + N,      # read words; write raw section + exponent plane
         "k_encode": N + C_ans,          # read exponent plane; write ANS archives
+        "k_coalesce": 2 * C_ans,        # read block slots; write ANS payload (extra pass, not algorithmic)
         "k_decode": C_total + U,        # read archives; write words
     }
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from `ncu --set full`
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("dram_bytes_per_launch", {})
     roofline = None
     if kern:
         top = max(kern, key=lambda k: kern[k][1])
@@ -314,7 +319,7 @@ def main():
         if top in alg and ms > 0:
             ach = alg[top] / (ms / cnt * 1e-3) / 1e9
             roofline = {"bound": "hbm", "kernel": top, "achieved": round(ach, 1), "peak": peak,
-                        "peak_kind": peak_kind, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                        "peak_kind": peak_kind, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": traffic.get(top),
                         "algorithmic_bytes_per_launch": alg[top], "avg_launch_ms": round(ms / cnt, 4)}
     phase = {
         "compress_GBps_uncompressed": round(comp_gbps, 1),

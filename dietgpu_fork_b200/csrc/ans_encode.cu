@@ -189,22 +189,28 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
 // symbol s throughout. Instead of physically sorting we compute each symbol's rank in the
 // descending order of (q << 16 | s): the reference's "positions" are these ranks.
 //
-// Encode-table entry (ours): x = magic, y = (2^probBits - pdf) | shift << 12 | cdf << 17 with
-// floor(v / pdf) == (umulhi(v, magic) + v) >> shift for v < 2^31. Storing K - pdf serves both the
-// renormalisation test (v >= pdf << (31 - probBits)  <=>  bit 31 of v + ((K - pdf) << (31 - probBits)))
-// and the state update v' = q * (K - pdf) + v + cdf; shift sits where a wrapping funnel shift can
-// take it from y >> 12 without masking. Absent symbols (pdf 0) get an all-zero entry.
+// Encode-table entry (ours, 16 bytes): x = magic m, y = pdf << (31 - probBits) (the renormalisation
+// threshold, :61-66), z = 2^probBits - pdf, w = cdf' << 17 | shift, such that for every state v the
+// encoder can hold when it divides (v < pdf << (31 - probBits), i.e. after renormalisation)
+//     floor(v / pdf) == umulhi(v, m) >> shift
+// and the update is v' = q * (2^probBits - pdf) + v + cdf'. For pdf >= 2: l = ceil(log2 pdf),
+// m = ceil(2^(31 + l) / pdf) <= 2^32 - 1 (2^31 for a power of two), shift = l - 1; the error term
+// e = m * pdf - 2^(31 + l) < pdf gives v * e < pdf^2 << (31 - probBits) <= 2^(31 + l), so the quotient
+// is exact. pdf == 1: m = 2^32 - 1 yields q = v - 1 (v >= 32 here), compensated by
+// cdf' = cdf + 2^probBits - 1; otherwise cdf' = cdf. The shift sits in the low 5 bits of w, where a
+// wrapping funnel shift reads it without masking, and cdf' in the high bits, where a single
+// shift-right-add (LEA.HI) extracts and adds it. Absent symbols (pdf 0) get an all-zero entry.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elems,
                                                    const uint32_t* __restrict__ nDev,
                                                    const uint32_t* __restrict__ hist, int probBits,
-                                                   uint2* __restrict__ table, uint32_t elemBegin) {
+                                                   uint4* __restrict__ table, uint32_t elemBegin) {
   __shared__ uint32_t sKey[256];
   __shared__ uint32_t sWarp[8];
   const uint32_t e = elemBegin + blockIdx.x, s = threadIdx.x, lane = s & 31, w = s >> 5;
   const uint32_t total = nDev ? nDev[e] : elems[e].n;
   if (total == 0) { // reference leaves the table untouched (:192-195); we define it as zero
-    table[e * 256 + s] = make_uint2(0, 0);
+    table[e * 256 + s] = make_uint4(0, 0, 0, 0);
     return;
   }
   const uint32_t count = hist[e * 256 + s];
@@ -259,12 +265,16 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
   uint32_t cdf = inc - q;
   for (uint32_t i = 0; i < w; ++i) cdf += sWarp[i];
 
-  uint2 entry = make_uint2(0, 0);
+  uint4 entry = make_uint4(0, 0, 0, 0);
   if (q) {
-    uint32_t shift = 32 - __clz(q - 1); // q == 1 -> clz(0) == 32 -> 0
-    uint64_t magic = ((1ull << 32) * ((1ull << shift) - q)) / q + 1; // :343-366
-    entry.x = (uint32_t)magic;
-    entry.y = (weight - q) | (shift << 12) | (cdf << 17);
+    const uint32_t l = 32 - __clz(q - 1); // q == 1 -> clz(0) == 32 -> 0
+    uint32_t m = 0xffffffffu, shift = 0, cdfAdj = cdf + weight - 1;
+    if (q > 1) {
+      m = (uint32_t)(((1ull << (31 + l)) + q - 1) / q);
+      shift = l - 1;
+      cdfAdj = cdf;
+    }
+    entry = make_uint4(m, q << (31 - probBits), weight - q, (cdfAdj << 17) | shift);
   }
   table[e * 256 + s] = entry;
 }
@@ -273,18 +283,19 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 // Block encoder + compaction (two kernels).
 //
 // k_encode: one autonomous warp per 4096-symbol ANS block, no CTA-wide barrier, no waiting on
-// other warps.
-//   symbols: 512-byte chunks (16 symbol rows) pulled into a 4-deep per-warp shared-memory ring by
-//            cp.async.bulk (TMA 1-D) + mbarrier, issued 4 chunks ahead of their use
-//   table:   the element's 2 KB encode table, read through L1
-//   rows:    rANS step per 32 symbols, ballot/popc compaction into a 1 KB per-warp staging buffer
-//   flush:   after every chunk the staged words go, as 16-byte vectors, to the block's slot of a
-//            scratch area; final lane states go straight into the archive, the word count into
-//            a per-block size array
-// k_coalesce: per tile of 8 blocks, a warp-shuffle / decoupled look-back exclusive scan of the
-// per-block sizes (roundUp(words, 8)) gives every block its final offset; the payload is copied
-// from the scratch slots (L2-resident: just written) to its final place together with the block
-// index, the pdf table and the header.
+// other warps, no shared-memory input staging.
+//   symbols: one byte load per lane and symbol row straight from global memory (a row is one
+//            32-byte sector, four rows share an L1 line), issued a whole 8-row batch ahead of use
+//   table:   the element's 4 KB encode table, read through L1, four rows ahead of use
+//   rows:    rANS step per 32 symbols (13 instructions), ballot/popc compaction into a 2.5 KB
+//            per-warp staging buffer
+//   flush:   the staged words go, as 16-byte vectors, to the block's slot of a scratch area when
+//            the block ends (typical data: once per block) or when the buffer could overflow
+//            within the next batch; final lane states go straight into the archive, the word
+//            count into a per-block size array
+// k_coalesce: every size is known when it starts; per tile of 8 blocks it sums the sizes before
+// the tile and copies the payload from the scratch slots (L2-resident: just written) to its final
+// place together with the block index, the pdf table and the header.
 //
 // Why not a single pass: a block's final offset is known only when ALL earlier blocks of the
 // element are encoded, i.e. after the slowest of them; measured on B200, warps spent as long
@@ -293,7 +304,7 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 // ---------------------------------------------------------------------------------------------
 struct EncParams {
   EncodeArgs a;
-  const uint2* table;   // [numElems][256]
+  const uint4* table;   // [numElems][256]
   uint8_t* scratch;     // [totalBlocks][kSlotBytes]
   uint32_t* blockWords; // [totalBlocks] words emitted per block
   uint32_t* groupWords; // [totalGroups] sum of roundUp(words, 8) per group of 256 blocks, zeroed
@@ -303,51 +314,46 @@ struct EncParams {
 };
 
 constexpr uint32_t kEncWarps = 4;
-constexpr uint32_t kGroupBlocks = 256;          // compaction: blocks per size group
-constexpr uint32_t kRingSlots = 4;
-constexpr uint32_t kChunk = 512;                 // symbols per ring slot = 16 rows
-constexpr uint32_t kEncStageBytes = 1024 + 32;   // 16 rows x 64 B + carry
+constexpr uint32_t kEncCtasPerSm = 10;
+constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
+constexpr uint32_t kEncBatchRows = 8;
+constexpr uint32_t kEncStageBytes = 2560;
+constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncBatchRows * 64; // room for one more batch, worst case
 constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
-constexpr uint32_t kEncWarpSmem = kRingSlots * kChunk + kEncStageBytes + 32;
+constexpr uint32_t kEncWarpSmem = kEncStageBytes;
 
 // One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
-// {magic, (K - pdf) | shift << 12 | cdf << 17}; outPtr = shared-memory byte address of the next
-// free staging word. Written in PTX to pin the instruction selection (~19 instructions).
-template <int PB>
-__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask) {
+// {m, pdf << (31 - PB), K - pdf, cdf' << 17 | shift}; outPtr = shared-memory byte address of the next
+// free staging word. Written in PTX to pin the instruction selection.
+__device__ __forceinline__ void encStep(uint32_t& state, uint4 e, uint32_t& outPtr, uint32_t ltMask) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      ".reg .b32 sum, vote, pre, addr, t, q, c, k;\n"
-      "mad.lo.u32 sum, %3, %5, %0;\n"          // ((K - pdf) << (31 - PB)) + state: bit 31 <=> renormalise
-      "setp.lt.s32 p, sum, 0;\n"
+      ".reg .b32 vote, pre, addr, t, q, c;\n"
+      "setp.ge.u32 p, %0, %3;\n"               // state >= pdf << (31 - PB): renormalise
       "vote.sync.ballot.b32 vote, p, 0xffffffff;\n"
-      "and.b32 pre, vote, %4;\n"
+      "and.b32 pre, vote, %6;\n"
       "popc.b32 pre, pre;\n"
       "mad.lo.u32 addr, pre, 2, %1;\n"
       "@p st.shared.u16 [addr], %0;\n"
       "@p shr.u32 %0, %0, 16;\n"
       "popc.b32 t, vote;\n"
       "mad.lo.u32 %1, t, 2, %1;\n"
-      "mul.hi.u32 t, %0, %2;\n"
-      "add.u32 t, t, %0;\n"
-      "shr.u32 c, %3, 12;\n"
-      "shf.r.wrap.b32 q, t, 0, c;\n"           // floor(state / pdf)
-      "and.b32 k, %3, 0xfff;\n"
-      "shr.u32 c, %3, 17;\n"
-      "add.u32 c, c, %0;\n"                    // state + cdf
-      "mad.lo.u32 %0, q, k, c;\n"              // q * (K - pdf) + state + cdf
+      "mul.hi.u32 q, %0, %2;\n"
+      "shf.r.wrap.b32 q, q, 0, %5;\n"          // floor(state / pdf)
+      "shr.u32 c, %5, 17;\n"
+      "add.u32 c, c, %0;\n"                    // state + cdf'
+      "mad.lo.u32 %0, q, %4, c;\n"             // q * (K - pdf) + state + cdf'
       "}\n"
       : "+r"(state), "+r"(outPtr)
-      : "r"(e.x), "r"(e.y), "r"(ltMask), "n"(1u << (31 - PB))
+      : "r"(e.x), "r"(e.y), "r"(e.z), "r"(e.w), "r"(ltMask)
       : "memory");
 }
 
 // partial last row: lanes >= rem neither emit nor update (:94-136)
-template <int PB>
-__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask,
+__device__ __forceinline__ void encStepPartial(uint32_t& state, uint4 e, uint32_t& outPtr, uint32_t ltMask,
                                                bool valid) {
-  const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
+  const bool wr = valid && state >= e.y;
   const uint32_t vote = __ballot_sync(0xffffffffu, wr);
   if (wr) {
     uint32_t addr = outPtr + 2u * __popc(vote & ltMask);
@@ -355,42 +361,43 @@ __device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_
     state >>= 16;
   }
   outPtr += 2u * __popc(vote);
-  const uint32_t q = __funnelshift_r(__umulhi(state, e.x) + state, 0u, e.y >> 12);
-  const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
+  const uint32_t q = __funnelshift_r(__umulhi(state, e.x), 0u, e.w);
+  const uint32_t ns = q * e.z + state + (e.w >> 17);
   state = valid ? ns : state;
 }
 
-template <int PB>
-__global__ void __launch_bounds__(kEncWarps * 32, 10) k_encode(const EncParams p) {
+__device__ __forceinline__ uint32_t ldSym(const uint8_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+__global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  uint8_t* ws = smem + w * kEncWarpSmem;
-  uint8_t* ring = ws;                        // kRingSlots * kChunk
-  uint8_t* stage = ws + kRingSlots * kChunk; // kEncStageBytes
-  const uint32_t bar0 = smemAddr(stage + kEncStageBytes); // kRingSlots mbarriers
-  const uint32_t ringAddr = smemAddr(ring), stageAddr = smemAddr(stage);
+  uint8_t* stage = smem + w * kEncWarpSmem;
+  const uint32_t stageAddr = smemAddr(stage);
   const uint32_t ltMask = laneMaskLt();
   const EncodeArgs& a = p.a;
-
-  if (lane == 0) {
-#pragma unroll
-    for (uint32_t s = 0; s < kRingSlots; ++s) mbarInit(bar0 + 8 * s, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncwarp();
-  uint32_t phaseBits = 0; // parity expected at the next wait on each slot
   uint32_t guess = 0;
 
   // blocks are independent here: static striding, so at any moment the resident warps stream one
   // contiguous window of the input (contiguous per-warp ranges measured 7 % slower on B200)
-  uint32_t curElem = 0xffffffffu, n = 0, nb = 0;
-  Elem el;
+  uint32_t curElem = 0xffffffffu, n = 0, nb = 0, blockBase = 0, nextBase = 0;
+  uint32_t* groupSum = nullptr;
+  const uint8_t* elemSrc = nullptr;
+  const uint4* tab = nullptr;
   uint8_t* ans = nullptr;
   for (uint32_t gb = p.blkBegin + blockIdx.x * kEncWarps + w; gb < p.blkEnd; gb += p.totalWarps) {
-    if (curElem == 0xffffffffu || gb >= a.elems[curElem + 1].blockBase) {
+    if (curElem == 0xffffffffu || gb >= nextBase) {
       curElem = findElement(&a.elems[0].blockBase, sizeof(Elem) / 4, a.numElems, gb, guess);
       guess = curElem;
-      el = a.elems[curElem];
+      const Elem el = a.elems[curElem];
+      nextBase = a.elems[curElem + 1].blockBase;
+      blockBase = el.blockBase;
+      groupSum = p.groupWords + el.groupBase;
+      elemSrc = (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + lane;
+      tab = p.table + (size_t)curElem * 256;
       n = a.nDev ? a.nDev[curElem] : el.n;
       nb = divUp(n, kBlockSyms);
       ans = (uint8_t*)el.out;
@@ -400,111 +407,91 @@ __global__ void __launch_bounds__(kEncWarps * 32, 10) k_encode(const EncParams p
         if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
       }
     }
-    const uint32_t e = curElem;
-    const uint32_t blk = gb - el.blockBase;
+    const uint32_t blk = gb - blockBase;
     if (blk >= nb) { // empty element, or the device-side size is smaller than the host bound
       if (lane == 0) p.blockWords[gb] = 0;
       continue;
     }
     const uint32_t blkLen = min(kBlockSyms, n - blk * kBlockSyms);
-    const uint8_t* src =
-        (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + (size_t)blk * kBlockSyms;
-    const uint32_t numChunks = divUp(blkLen, kChunk);
-    const bool bulk = (((uintptr_t)src) & 15u) == 0;
-    uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
-    const uint2* __restrict__ tab = p.table + (size_t)e * 256;
-
-    auto issueChunk = [&](uint32_t c) {
-      const uint32_t sl = c & (kRingSlots - 1);
-      const uint32_t len = min(kChunk, blkLen - c * kChunk);
-      if (bulk) {
-        if (lane == 0) {
-          const uint32_t bytes = roundUp(len, 16);
-          mbarExpectTx(bar0 + 8 * sl, bytes);
-          bulkLoad(ringAddr + sl * kChunk, src + c * kChunk, bytes, bar0 + 8 * sl);
-        }
-      } else { // unaligned input: plain loads (4-byte words when possible)
-        const uint8_t* g = src + c * kChunk + lane * 16;
-        uint8_t* d = ring + sl * kChunk + lane * 16;
-        if ((((uintptr_t)g) & 3u) == 0 && lane * 16 + 16 <= len) {
-          const uint32_t* g4 = (const uint32_t*)g;
-          *(uint4*)d = make_uint4(g4[0], g4[1], g4[2], g4[3]);
-        } else {
-#pragma unroll
-          for (int k = 0; k < 16; ++k)
-            if (lane * 16 + k < len) d[k] = g[k];
-        }
-      }
-    };
-    __syncwarp();
-    for (uint32_t c = 0; c < min(numChunks, kRingSlots); ++c) issueChunk(c);
+    const uint8_t* src = elemSrc + (size_t)blk * kBlockSyms;
 
     uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
-    for (uint32_t c = 0; c < numChunks; ++c) {
-      const uint32_t sl = c & (kRingSlots - 1);
-      if (bulk) {
-        mbarWait(bar0 + 8 * sl, (phaseBits >> sl) & 1u);
-        phaseBits ^= 1u << sl;
-      } else {
-        __syncwarp();
-      }
-      const uint32_t symAddr = ringAddr + sl * kChunk + lane;
-      const uint32_t len = min(kChunk, blkLen - c * kChunk);
-      if (len == kChunk) {
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint2 ent[8];
-#pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            uint32_t sym;
-            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + (half * 8 + r) * 32));
-            ent[r] = __ldg(tab + sym);
-          }
-#pragma unroll
-          for (int r = 0; r < 8; ++r) encStep<PB>(state, ent[r], outPtr, ltMask);
-        }
-      } else {
-        const uint32_t rows = len >> 5, rem = len & 31u;
-        for (uint32_t r = 0; r < rows; ++r) {
-          uint32_t sym;
-          asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + r * 32));
-          encStep<PB>(state, __ldg(tab + sym), outPtr, ltMask);
-        }
-        if (rem) {
-          const bool valid = lane < rem;
-          uint32_t sym = 0;
-          if (valid) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sym) : "r"(symAddr + rows * 32));
-          encStepPartial<PB>(state, __ldg(tab + sym), outPtr, ltMask, valid);
-        }
-      }
-      __syncwarp();
-      // this ring slot is consumed: refill it with the chunk kRingSlots ahead
-      if (c + kRingSlots < numChunks) issueChunk(c + kRingSlots);
-      // flush the staged words: whole 16-byte vectors go to the scratch slot, the rest is carried
+    // staged words -> scratch slot. final: pad with zero words to a multiple of 8 words and publish the
+    // sizes; otherwise whole 16-byte vectors go out and the remainder moves to the front of the buffer
+    auto flush = [&](bool final) {
+      uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
       uint32_t bytes = outPtr - stageAddr;
-      if (c + 1 == numChunks) { // last chunk: pad with zero words to a multiple of 8 words
+      __syncwarp();
+      if (final) {
         const uint32_t padded = roundUp(bytes, 16);
         if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
         __syncwarp();
         if (lane == 0) {
           p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
-          atomicAdd(&p.groupWords[el.groupBase + blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
+          atomicAdd(&groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
         }
         bytes = padded;
       }
       const uint32_t nv = bytes >> 4;
       for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
-      const uint32_t remBytes = bytes & 15u;
-      uint32_t carry = 0;
-      if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
-      __syncwarp();
-      if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
-      __syncwarp();
-      flushedVecs += nv;
-      outPtr = stageAddr + remBytes;
+      if (!final) {
+        const uint32_t remBytes = bytes & 15u;
+        uint32_t carry = 0;
+        if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
+        __syncwarp();
+        if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
+        __syncwarp();
+        flushedVecs += nv;
+        outPtr = stageAddr + remBytes;
+      }
+    };
+
+    const uint32_t rows = blkLen >> 5, rem = blkLen & 31u;
+    const uint32_t batches = rows / kEncBatchRows;
+    if (batches) {
+      // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
+      // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
+      // symbol of row r + 10. Symbols are thus requested 8 rows (>= 128 issue slots x resident warps)
+      // before the dependent table load, table entries 2 rows before their step.
+      uint32_t sym[8];
+      uint4 ent[2];
+      ent[0] = __ldg(tab + ldSym(src));
+      ent[1] = __ldg(tab + ldSym(src + 32));
+#pragma unroll
+      for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
+      sym[0] = sym[1] = 0;
+      if (batches > 1) {
+        sym[0] = ldSym(src + 8 * 32);
+        sym[1] = ldSym(src + 9 * 32);
+      }
+      const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
+      for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
+        const bool p1 = b + 1 < batches, p2 = b + 2 < batches;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          encStep(state, ent[i & 1], outPtr, ltMask);
+          ent[i & 1] = __ldg(tab + sym[(i + 2) & 7]);
+          if (i < 6 ? p1 : p2) sym[(i + 2) & 7] = ldSym(nx + i * 32);
+        }
+        if (p1 && outPtr - stageAddr >= kEncFlushAt) flush(false);
+      }
     }
+    // last block of an element: leftover rows and the partial row
+    if (rows % kEncBatchRows || rem) {
+      if (outPtr - stageAddr >= kEncFlushAt) flush(false);
+      const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
+      for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
+        encStep(state, __ldg(tab + ldSym(tail + r * 32)), outPtr, ltMask);
+      if (rem) {
+        const bool valid = lane < rem;
+        const uint32_t sym = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
+        encStepPartial(state, __ldg(tab + sym), outPtr, ltMask, valid);
+      }
+    }
+    flush(true);
     // final lane states go straight to their place in the archive (:584-589)
     ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
+    __syncwarp(); // the staging buffer is reused by the next block
   }
 }
 
@@ -571,8 +558,8 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
     for (uint32_t i = lane; i < nv; i += 32) dst[i] = src[i];
   }
   if (t == 0) { // pdf table (:568-573); zero for absent symbols and for an empty element
-    const uint2 en = p.table[(size_t)e * 256 + tid];
-    const uint32_t pdf = (n && en.x) ? (1u << probBits) - (en.y & 0xfffu) : 0u;
+    const uint4 en = p.table[(size_t)e * 256 + tid];
+    const uint32_t pdf = (n && en.x) ? (1u << probBits) - en.z : 0u;
     ((uint16_t*)(ans + kAnsHeaderBytes))[tid] = (uint16_t)pdf;
   }
   if (t == numTiles - 1 && tid == 0) {
@@ -595,7 +582,7 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
 }
 
 int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s) {
-  es.table = tmp.alloc<uint2>((size_t)a.numElems * 256);
+  es.table = tmp.alloc<uint4>((size_t)a.numElems * 256);
   es.blockWords = tmp.alloc<uint32_t>(a.totalTiles);
   es.groupWords = tmp.alloc<uint32_t>(totalGroups);
   es.scratch = (uint8_t*)tmp.alloc((size_t)a.totalTiles * kSlotBytes);
@@ -623,24 +610,14 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   p.blkEnd = r.blk1;
   p.tileBegin = r.tile0;
   const uint32_t blocks = r.blk1 - r.blk0;
-  const uint32_t grid = min(divUp(blocks, kEncWarps), (uint32_t)smCount() * 10u);
+  const uint32_t grid = min(divUp(blocks, kEncWarps), (uint32_t)smCount() * kEncCtasPerSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
-  auto launch = [&](auto kern) -> int {
-    {
-      ProfScope ps__("k_encode", s);
-      kern<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
-    }
-    DGB_CUDA(cudaGetLastError());
-    return kOk;
-  };
-  int rc;
-  switch (a.probBits) {
-    case 9: rc = launch(k_encode<9>); break;
-    case 10: rc = launch(k_encode<10>); break;
-    default: rc = launch(k_encode<11>); break;
+  {
+    ProfScope ps__("k_encode", s);
+    k_encode<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
   }
-  if (rc) return rc;
+  DGB_CUDA(cudaGetLastError());
   {
     ProfScope ps__("k_coalesce", s);
     k_coalesce<<<r.tile1 - r.tile0, 256, 0, s>>>(p, a.probBits);

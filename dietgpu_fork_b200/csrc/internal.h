@@ -136,7 +136,7 @@ struct WorkRange {
 };
 // Scratch of one encode pass (one exponent plane / byte stream) over the whole work list.
 struct EncodeScratch {
-  uint2* table;
+  uint4* table;
   uint32_t* blockWords;
   uint32_t* groupWords;
   uint8_t* scratch;

@@ -1,0 +1,18 @@
+#!/bin/bash
+# One GPU box visit: parity tests, smoke, both bench arms, then the ncu launch list of the bench command.
+# Usage (from the repo root, through gpurun): bash scripts/gpu_round.sh <tag>
+set -u
+tag=${1:-run}
+mkdir -p gpurun_out
+python -m pytest tests -x -q -m gpu > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" | tee gpurun_out/${tag}_rc.log
+tail -3 gpurun_out/${tag}_pytest.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/${tag}_rc.log
+python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "bench ref rc=$?" | tee -a gpurun_out/${tag}_rc.log
+python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; rc=$?; echo "bench rc=$rc" | tee -a gpurun_out/${tag}_rc.log
+tail -1 gpurun_out/${tag}_bench_ref.json | cut -c1-1500
+tail -1 gpurun_out/${tag}_bench.json
+if [ $rc -eq 0 ]; then
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_ncu.log 2>&1
+  echo "ncu rc=$?" | tee -a gpurun_out/${tag}_rc.log
+fi
