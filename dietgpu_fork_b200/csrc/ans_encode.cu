@@ -189,28 +189,29 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
 // symbol s throughout. Instead of physically sorting we compute each symbol's rank in the
 // descending order of (q << 16 | s): the reference's "positions" are these ranks.
 //
-// Encode-table entry (ours, 16 bytes): x = magic m, y = pdf << (31 - probBits) (the renormalisation
-// threshold, :61-66), z = 2^probBits - pdf, w = cdf' << 17 | shift, such that for every state v the
-// encoder can hold when it divides (v < pdf << (31 - probBits), i.e. after renormalisation)
+// Encode-table entry (ours, 8 bytes): x = magic m, y = (2^probBits - pdf) | shift << 12 | cdf' << 17,
+// such that for every state v the encoder can hold when it divides (v < pdf << (31 - probBits), i.e.
+// after renormalisation)
 //     floor(v / pdf) == umulhi(v, m) >> shift
 // and the update is v' = q * (2^probBits - pdf) + v + cdf'. For pdf >= 2: l = ceil(log2 pdf),
 // m = ceil(2^(31 + l) / pdf) <= 2^32 - 1 (2^31 for a power of two), shift = l - 1; the error term
 // e = m * pdf - 2^(31 + l) < pdf gives v * e < pdf^2 << (31 - probBits) <= 2^(31 + l), so the quotient
 // is exact. pdf == 1: m = 2^32 - 1 yields q = v - 1 (v >= 32 here), compensated by
-// cdf' = cdf + 2^probBits - 1; otherwise cdf' = cdf. The shift sits in the low 5 bits of w, where a
-// wrapping funnel shift reads it without masking, and cdf' in the high bits, where a single
+// cdf' = cdf + 2^probBits - 1; otherwise cdf' = cdf. Storing K - pdf in the low bits serves both the
+// renormalisation test (v >= pdf << (31 - probBits)  <=>  bit 31 of v + (y << (31 - probBits)), the
+// multiply drops every other field) and the update; cdf' sits in the high bits, where a single
 // shift-right-add (LEA.HI) extracts and adds it. Absent symbols (pdf 0) get an all-zero entry.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elems,
                                                    const uint32_t* __restrict__ nDev,
                                                    const uint32_t* __restrict__ hist, int probBits,
-                                                   uint4* __restrict__ table, uint32_t elemBegin) {
+                                                   uint2* __restrict__ table, uint32_t elemBegin) {
   __shared__ uint32_t sKey[256];
   __shared__ uint32_t sWarp[8];
   const uint32_t e = elemBegin + blockIdx.x, s = threadIdx.x, lane = s & 31, w = s >> 5;
   const uint32_t total = nDev ? nDev[e] : elems[e].n;
   if (total == 0) { // reference leaves the table untouched (:192-195); we define it as zero
-    table[e * 256 + s] = make_uint4(0, 0, 0, 0);
+    table[e * 256 + s] = make_uint2(0, 0);
     return;
   }
   const uint32_t count = hist[e * 256 + s];
@@ -265,7 +266,7 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
   uint32_t cdf = inc - q;
   for (uint32_t i = 0; i < w; ++i) cdf += sWarp[i];
 
-  uint4 entry = make_uint4(0, 0, 0, 0);
+  uint2 entry = make_uint2(0, 0);
   if (q) {
     const uint32_t l = 32 - __clz(q - 1); // q == 1 -> clz(0) == 32 -> 0
     uint32_t m = 0xffffffffu, shift = 0, cdfAdj = cdf + weight - 1;
@@ -274,7 +275,7 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
       shift = l - 1;
       cdfAdj = cdf;
     }
-    entry = make_uint4(m, q << (31 - probBits), weight - q, (cdfAdj << 17) | shift);
+    entry = make_uint2(m, (weight - q) | (shift << 12) | (cdfAdj << 17));
   }
   table[e * 256 + s] = entry;
 }
@@ -304,35 +305,40 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 // ---------------------------------------------------------------------------------------------
 struct EncParams {
   EncodeArgs a;
-  const uint4* table;   // [numElems][256]
+  const uint2* table;   // [numElems][256]
   uint8_t* scratch;     // [totalBlocks][kSlotBytes]
   uint32_t* blockWords; // [totalBlocks] words emitted per block
   uint32_t* groupWords; // [totalGroups] sum of roundUp(words, 8) per group of 256 blocks, zeroed
+  uint32_t* runCounter;  // zeroed; hands out runs beyond each warp's first one
   uint32_t totalWarps;
-  uint32_t blkBegin, blkEnd; // range of blocks handled by this k_encode launch
-  uint32_t tileBegin;        // first 8-block tile handled by this k_coalesce launch
+  uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
 };
 
 constexpr uint32_t kEncWarps = 4;
 constexpr uint32_t kEncCtasPerSm = 10;
 constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
 constexpr uint32_t kEncBatchRows = 8;
+constexpr uint32_t kRunBlocks = 4;              // consecutive blocks one warp encodes as one stream (half a tile)
+constexpr uint32_t kBlockBatches = kBlockSyms / (32 * kEncBatchRows);
+constexpr uint32_t kEncTableBytes = 256 * 8;     // per-warp copy of the element's encode table
 constexpr uint32_t kEncStageBytes = 2560;
 constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncBatchRows * 64; // room for one more batch, worst case
 constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
-constexpr uint32_t kEncWarpSmem = kEncStageBytes;
+constexpr uint32_t kEncWarpSmem = kEncTableBytes + kEncStageBytes;
 
 // One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
-// {m, pdf << (31 - PB), K - pdf, cdf' << 17 | shift}; outPtr = shared-memory byte address of the next
-// free staging word. Written in PTX to pin the instruction selection.
-__device__ __forceinline__ void encStep(uint32_t& state, uint4 e, uint32_t& outPtr, uint32_t ltMask) {
+// {m, (K - pdf) | shift << 12 | cdf' << 17}; outPtr = shared-memory byte address of the next free
+// staging word. Written in PTX to pin the instruction selection.
+template <int PB>
+__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      ".reg .b32 vote, pre, addr, t, q, c;\n"
-      "setp.ge.u32 p, %0, %3;\n"               // state >= pdf << (31 - PB): renormalise
+      ".reg .b32 sum, vote, pre, addr, t, q, c, k;\n"
+      "mad.lo.u32 sum, %3, %5, %0;\n"          // ((K - pdf) << (31 - PB)) + state: bit 31 <=> renormalise
+      "setp.lt.s32 p, sum, 0;\n"
       "vote.sync.ballot.b32 vote, p, 0xffffffff;\n"
-      "and.b32 pre, vote, %6;\n"
+      "and.b32 pre, vote, %4;\n"
       "popc.b32 pre, pre;\n"
       "mad.lo.u32 addr, pre, 2, %1;\n"
       "@p st.shared.u16 [addr], %0;\n"
@@ -340,20 +346,23 @@ __device__ __forceinline__ void encStep(uint32_t& state, uint4 e, uint32_t& outP
       "popc.b32 t, vote;\n"
       "mad.lo.u32 %1, t, 2, %1;\n"
       "mul.hi.u32 q, %0, %2;\n"
-      "shf.r.wrap.b32 q, q, 0, %5;\n"          // floor(state / pdf)
-      "shr.u32 c, %5, 17;\n"
+      "shr.u32 c, %3, 12;\n"
+      "shf.r.wrap.b32 q, q, 0, c;\n"           // floor(state / pdf)
+      "and.b32 k, %3, 0xfff;\n"
+      "shr.u32 c, %3, 17;\n"
       "add.u32 c, c, %0;\n"                    // state + cdf'
-      "mad.lo.u32 %0, q, %4, c;\n"             // q * (K - pdf) + state + cdf'
+      "mad.lo.u32 %0, q, k, c;\n"              // q * (K - pdf) + state + cdf'
       "}\n"
       : "+r"(state), "+r"(outPtr)
-      : "r"(e.x), "r"(e.y), "r"(e.z), "r"(e.w), "r"(ltMask)
+      : "r"(e.x), "r"(e.y), "r"(ltMask), "n"(1u << (31 - PB))
       : "memory");
 }
 
 // partial last row: lanes >= rem neither emit nor update (:94-136)
-__device__ __forceinline__ void encStepPartial(uint32_t& state, uint4 e, uint32_t& outPtr, uint32_t ltMask,
+template <int PB>
+__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask,
                                                bool valid) {
-  const bool wr = valid && state >= e.y;
+  const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
   const uint32_t vote = __ballot_sync(0xffffffffu, wr);
   if (wr) {
     uint32_t addr = outPtr + 2u * __popc(vote & ltMask);
@@ -361,43 +370,65 @@ __device__ __forceinline__ void encStepPartial(uint32_t& state, uint4 e, uint32_
     state >>= 16;
   }
   outPtr += 2u * __popc(vote);
-  const uint32_t q = __funnelshift_r(__umulhi(state, e.x), 0u, e.w);
-  const uint32_t ns = q * e.z + state + (e.w >> 17);
+  const uint32_t q = __funnelshift_r(__umulhi(state, e.x), 0u, e.y >> 12);
+  const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
   state = valid ? ns : state;
 }
 
 __device__ __forceinline__ uint32_t ldSym(const uint8_t* p) {
   uint32_t v;
-  asm volatile("ld.global.nc.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  asm volatile("ld.global.nc.L2::256B.u8 %0, [%1];" : "=r"(v) : "l"(p));
   return v;
 }
 
+// table entry of symbol `sym` from the warp's shared-memory copy
+__device__ __forceinline__ uint2 ldEnt(uint32_t tabAddr, uint32_t sym) {
+  uint2 e;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(tabAddr + sym * 8));
+  return e;
+}
+
+template <int PB>
 __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  uint8_t* stage = smem + w * kEncWarpSmem;
-  const uint32_t stageAddr = smemAddr(stage);
+  uint8_t* tabSmem = smem + w * kEncWarpSmem;
+  uint8_t* stage = tabSmem + kEncTableBytes;
+  const uint32_t tabAddr = smemAddr(tabSmem), stageAddr = smemAddr(stage);
   const uint32_t ltMask = laneMaskLt();
   const EncodeArgs& a = p.a;
   uint32_t guess = 0;
 
-  // blocks are independent here: static striding, so at any moment the resident warps stream one
-  // contiguous window of the input (contiguous per-warp ranges measured 7 % slower on B200)
-  uint32_t curElem = 0xffffffffu, n = 0, nb = 0, blockBase = 0, nextBase = 0;
+  // Work unit = run of kRunBlocks consecutive blocks of one element (half of an 8-block tile): one
+  // element lookup and one uninterrupted symbol stream per run. A warp's first run is static, further
+  // runs are handed out in order by an atomic counter (fetched one run ahead), so the resident warps
+  // always stream one contiguous window of the input and finish together.
+  uint32_t curElem = 0xffffffffu, n = 0, nb = 0, blockBase = 0, tileBase = 0, nextTileBase = 0;
   uint32_t* groupSum = nullptr;
   const uint8_t* elemSrc = nullptr;
-  const uint4* tab = nullptr;
   uint8_t* ans = nullptr;
-  for (uint32_t gb = p.blkBegin + blockIdx.x * kEncWarps + w; gb < p.blkEnd; gb += p.totalWarps) {
-    if (curElem == 0xffffffffu || gb >= nextBase) {
-      curElem = findElement(&a.elems[0].blockBase, sizeof(Elem) / 4, a.numElems, gb, guess);
+  const uint32_t numRuns = (p.tileEnd - p.tileBegin) * (kTileBlocks / kRunBlocks);
+  uint32_t run = blockIdx.x * kEncWarps + w;
+  while (run < numRuns) {
+    uint32_t nextRun = 0;
+    if (lane == 0) nextRun = p.totalWarps + atomicAdd(p.runCounter, 1u);
+    const uint32_t tile = p.tileBegin + run / (kTileBlocks / kRunBlocks);
+    if (curElem == 0xffffffffu || tile >= nextTileBase || tile < tileBase) {
+      curElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, guess);
       guess = curElem;
       const Elem el = a.elems[curElem];
-      nextBase = a.elems[curElem + 1].blockBase;
+      nextTileBase = a.elems[curElem + 1].tileBase;
+      tileBase = el.tileBase;
       blockBase = el.blockBase;
       groupSum = p.groupWords + el.groupBase;
       elemSrc = (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + lane;
-      tab = p.table + (size_t)curElem * 256;
+      { // the element's 2 KB table -> this warp's shared-memory copy
+        const uint4* g = (const uint4*)(p.table + (size_t)curElem * 256);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ((uint4*)tabSmem)[lane + 32 * i] = g[lane + 32 * i];
+        __syncwarp();
+      }
       n = a.nDev ? a.nDev[curElem] : el.n;
       nb = divUp(n, kBlockSyms);
       ans = (uint8_t*)el.out;
@@ -407,91 +438,102 @@ __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const 
         if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
       }
     }
-    const uint32_t blk = gb - blockBase;
-    if (blk >= nb) { // empty element, or the device-side size is smaller than the host bound
-      if (lane == 0) p.blockWords[gb] = 0;
-      continue;
-    }
-    const uint32_t blkLen = min(kBlockSyms, n - blk * kBlockSyms);
-    const uint8_t* src = elemSrc + (size_t)blk * kBlockSyms;
+    uint32_t blk = (tile - tileBase) * kTileBlocks + (run % (kTileBlocks / kRunBlocks)) * kRunBlocks;
+    if (blk < nb) { // else: empty element, or the device-side size is smaller than the host bound
+      const uint32_t runSyms = min(n, (blk + kRunBlocks) * kBlockSyms) - blk * kBlockSyms;
+      const uint8_t* src = elemSrc + (size_t)blk * kBlockSyms;
 
-    uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
-    // staged words -> scratch slot. final: pad with zero words to a multiple of 8 words and publish the
-    // sizes; otherwise whole 16-byte vectors go out and the remainder moves to the front of the buffer
-    auto flush = [&](bool final) {
-      uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
-      uint32_t bytes = outPtr - stageAddr;
-      __syncwarp();
-      if (final) {
-        const uint32_t padded = roundUp(bytes, 16);
-        if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
+      uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
+      // staged words -> scratch slot of block `blk`. final: pad with zero words to a multiple of 8 words,
+      // publish the sizes and the lane states, reset for the next block; otherwise whole 16-byte vectors
+      // go out and the remainder moves to the front of the buffer
+      auto flush = [&](bool final) {
+        const uint32_t gb = blockBase + blk;
+        uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
+        uint32_t bytes = outPtr - stageAddr;
         __syncwarp();
-        if (lane == 0) {
-          p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
-          atomicAdd(&groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
+        if (final) {
+          const uint32_t padded = roundUp(bytes, 16);
+          if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
+          __syncwarp();
+          if (lane == 0) {
+            p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
+            atomicAdd(&groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
+          }
+          bytes = padded;
         }
-        bytes = padded;
-      }
-      const uint32_t nv = bytes >> 4;
-      for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
-      if (!final) {
-        const uint32_t remBytes = bytes & 15u;
-        uint32_t carry = 0;
-        if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
-        __syncwarp();
-        if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
-        __syncwarp();
-        flushedVecs += nv;
-        outPtr = stageAddr + remBytes;
-      }
-    };
+        const uint32_t nv = bytes >> 4;
+        for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
+        if (final) {
+          // final lane states go straight to their place in the archive (:584-589)
+          ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
+          __syncwarp(); // the staging buffer is reused by the next block
+          state = kStateMin;
+          outPtr = stageAddr;
+          flushedVecs = 0;
+          ++blk;
+        } else {
+          const uint32_t remBytes = bytes & 15u;
+          uint32_t carry = 0;
+          if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
+          __syncwarp();
+          if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
+          __syncwarp();
+          flushedVecs += nv;
+          outPtr = stageAddr + remBytes;
+        }
+      };
 
-    const uint32_t rows = blkLen >> 5, rem = blkLen & 31u;
-    const uint32_t batches = rows / kEncBatchRows;
-    if (batches) {
-      // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
-      // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
-      // symbol of row r + 10. Symbols are thus requested 8 rows (>= 128 issue slots x resident warps)
-      // before the dependent table load, table entries 2 rows before their step.
-      uint32_t sym[8];
-      uint4 ent[2];
-      ent[0] = __ldg(tab + ldSym(src));
-      ent[1] = __ldg(tab + ldSym(src + 32));
+      const uint32_t rows = runSyms >> 5, rem = runSyms & 31u;
+      const uint32_t batches = rows / kEncBatchRows;
+      if (batches) {
+        // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
+        // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
+        // symbol of row r + 10. Symbols are thus requested 8 rows (>= 150 issue slots x resident warps)
+        // before the dependent table load, table entries 2 rows before their step. The stream runs
+        // through block boundaries; only the state and the staging buffer are reset there.
+        uint32_t sym[8];
+        uint2 ent[2];
+        ent[0] = ldEnt(tabAddr, ldSym(src));
+        ent[1] = ldEnt(tabAddr, ldSym(src + 32));
 #pragma unroll
-      for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
-      sym[0] = sym[1] = 0;
-      if (batches > 1) {
-        sym[0] = ldSym(src + 8 * 32);
-        sym[1] = ldSym(src + 9 * 32);
-      }
-      const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
-      for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
-        const bool p1 = b + 1 < batches, p2 = b + 2 < batches;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          encStep(state, ent[i & 1], outPtr, ltMask);
-          ent[i & 1] = __ldg(tab + sym[(i + 2) & 7]);
-          if (i < 6 ? p1 : p2) sym[(i + 2) & 7] = ldSym(nx + i * 32);
+        for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
+        {
+          const uint8_t* ld = batches > 1 ? src + 8 * 32 : src;
+          sym[0] = ldSym(ld);
+          sym[1] = ldSym(ld + 32);
         }
-        if (p1 && outPtr - stageAddr >= kEncFlushAt) flush(false);
+        const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
+        for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
+          // rows past the end of the run are replaced by re-reads of its first rows (valid memory, the
+          // values are never used): the loads stay unconditional, so nothing waits on them here
+          const uint8_t* ld1 = b + 1 < batches ? nx : src;
+          const uint8_t* ld2 = b + 2 < batches ? nx : src;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            encStep<PB>(state, ent[i & 1], outPtr, ltMask);
+            ent[i & 1] = ldEnt(tabAddr, sym[(i + 2) & 7]);
+            sym[(i + 2) & 7] = ldSym((i < 6 ? ld1 : ld2) + i * 32);
+          }
+          if ((b & (kBlockBatches - 1)) == kBlockBatches - 1) flush(true);
+          else if (outPtr - stageAddr >= kEncFlushAt) flush(false);
+        }
       }
-    }
-    // last block of an element: leftover rows and the partial row
-    if (rows % kEncBatchRows || rem) {
-      if (outPtr - stageAddr >= kEncFlushAt) flush(false);
-      const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
-      for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
-        encStep(state, __ldg(tab + ldSym(tail + r * 32)), outPtr, ltMask);
-      if (rem) {
-        const bool valid = lane < rem;
-        const uint32_t sym = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
-        encStepPartial(state, __ldg(tab + sym), outPtr, ltMask, valid);
+      // last block of an element: leftover rows and the partial row
+      if (rows % kEncBatchRows || rem) {
+        if (outPtr - stageAddr >= kEncFlushAt) flush(false);
+        const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
+        for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
+          encStep<PB>(state, ldEnt(tabAddr, ldSym(tail + r * 32)), outPtr, ltMask);
+        if (rem) {
+          const bool valid = lane < rem;
+          const uint32_t sym = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
+          encStepPartial<PB>(state, ldEnt(tabAddr, sym), outPtr, ltMask, valid);
+        }
       }
+      if (runSyms & (kBlockSyms - 1)) flush(true); // the partial block
     }
-    flush(true);
-    // final lane states go straight to their place in the archive (:584-589)
-    ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
-    __syncwarp(); // the staging buffer is reused by the next block
+    run = __shfl_sync(0xffffffffu, nextRun, 0);
   }
 }
 
@@ -558,8 +600,8 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
     for (uint32_t i = lane; i < nv; i += 32) dst[i] = src[i];
   }
   if (t == 0) { // pdf table (:568-573); zero for absent symbols and for an empty element
-    const uint4 en = p.table[(size_t)e * 256 + tid];
-    const uint32_t pdf = (n && en.x) ? (1u << probBits) - en.z : 0u;
+    const uint2 en = p.table[(size_t)e * 256 + tid];
+    const uint32_t pdf = (n && en.x) ? (1u << probBits) - (en.y & 0xfffu) : 0u;
     ((uint16_t*)(ans + kAnsHeaderBytes))[tid] = (uint16_t)pdf;
   }
   if (t == numTiles - 1 && tid == 0) {
@@ -582,12 +624,13 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
 }
 
 int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s) {
-  es.table = tmp.alloc<uint4>((size_t)a.numElems * 256);
+  es.table = tmp.alloc<uint2>((size_t)a.numElems * 256);
   es.blockWords = tmp.alloc<uint32_t>(a.totalTiles);
-  es.groupWords = tmp.alloc<uint32_t>(totalGroups);
+  es.groupWords = tmp.alloc<uint32_t>(totalGroups + a.numElems + 1); // + one run counter per possible launch
   es.scratch = (uint8_t*)tmp.alloc((size_t)a.totalTiles * kSlotBytes);
   if (tmp.failed()) return kErrCuda;
-  DGB_CUDA(cudaMemsetAsync(es.groupWords, 0, (size_t)totalGroups * 4, s));
+  es.runCounters = es.groupWords + totalGroups;
+  DGB_CUDA(cudaMemsetAsync(es.groupWords, 0, (size_t)(totalGroups + a.numElems + 1) * 4, s));
   return kOk;
 }
 
@@ -606,18 +649,29 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   p.scratch = es.scratch;
   p.blockWords = es.blockWords;
   p.groupWords = es.groupWords;
-  p.blkBegin = r.blk0;
-  p.blkEnd = r.blk1;
+  p.runCounter = es.runCounters + r.e0;
   p.tileBegin = r.tile0;
-  const uint32_t blocks = r.blk1 - r.blk0;
-  const uint32_t grid = min(divUp(blocks, kEncWarps), (uint32_t)smCount() * kEncCtasPerSm);
+  p.tileEnd = r.tile1;
+  const uint32_t runs = (r.tile1 - r.tile0) * (kTileBlocks / kRunBlocks);
+  const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * kEncCtasPerSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
-  {
-    ProfScope ps__("k_encode", s);
-    k_encode<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
+  auto launch = [&](auto kern) -> int {
+    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    {
+      ProfScope ps__("k_encode", s);
+      kern<<<grid, kEncWarps * 32, smemBytes, s>>>(p);
+    }
+    DGB_CUDA(cudaGetLastError());
+    return kOk;
+  };
+  int rc;
+  switch (a.probBits) {
+    case 9: rc = launch(k_encode<9>); break;
+    case 10: rc = launch(k_encode<10>); break;
+    default: rc = launch(k_encode<11>); break;
   }
-  DGB_CUDA(cudaGetLastError());
+  if (rc) return rc;
   {
     ProfScope ps__("k_coalesce", s);
     k_coalesce<<<r.tile1 - r.tile0, 256, 0, s>>>(p, a.probBits);

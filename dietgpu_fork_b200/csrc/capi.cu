@@ -530,7 +530,7 @@ size_t dgb_temp_bytes_required(int op, int ft, uint32_t num, uint32_t maxSize) {
   const size_t spTiles = B * (divUp(maxSize, 8192) + 1);
   const size_t desc = (B + 1) * sizeof(Elem) + 512;
   const size_t blocks = B * (divUp(maxSize, kBlockSyms) + 1);
-  const size_t enc = B * 256 * 16 + tiles * 8 + blocks * (4 + 5632) + 2048; // tables, tile states, scratch slots
+  const size_t enc = B * 256 * 8 + tiles * 8 + B * 8 + blocks * (4 + 5632) + 2048; // tables, tile states, scratch slots
   const size_t dec = B * (sizeof(DecInfo) + (4u << 11)) * 2 + 1024;
   const size_t row = roundUpSz(maxSize, 16);
   const size_t wb = floatWordBytes(ft);

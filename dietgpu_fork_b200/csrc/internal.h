@@ -136,9 +136,10 @@ struct WorkRange {
 };
 // Scratch of one encode pass (one exponent plane / byte stream) over the whole work list.
 struct EncodeScratch {
-  uint4* table;
+  uint2* table;
   uint32_t* blockWords;
   uint32_t* groupWords;
+  uint32_t* runCounters;
   uint8_t* scratch;
 };
 // totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
