@@ -11,6 +11,8 @@
 // kernel stages a tile of 8 blocks in shared memory, encodes it with 8 warps, obtains the tile's
 // output offset with a decoupled look-back over tile aggregates and writes states, block index
 // and payload straight to their final place; the last tile of an element writes the header.
+#include <cstdlib>
+
 #include "internal.h"
 #include "prof.h"
 
@@ -653,7 +655,9 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   p.tileBegin = r.tile0;
   p.tileEnd = r.tile1;
   const uint32_t runs = (r.tile1 - r.tile0) * (kTileBlocks / kRunBlocks);
-  const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * kEncCtasPerSm);
+  uint32_t perSm = kEncCtasPerSm;
+  if (const char* e = getenv("DGB_ENC_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
+  const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * perSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
   auto launch = [&](auto kern) -> int {

@@ -6,6 +6,8 @@
 // in how: every CTA owns a contiguous range of 32768-word tiles, each thread handles one 16-byte
 // input vector per step with warp-contiguous loads and stores, histograms live in per-warp 4-way
 // replicated shared-memory bins, and all padding the reference leaves undefined is written as 0.
+#include <cstdlib>
+
 #include "float_math.cuh"
 #include "internal.h"
 #include "prof.h"
@@ -180,7 +182,9 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
   constexpr uint32_t smemBytes = FloatTraits<FT>::kPlanes * kSplitHistWords * 4;
   DGB_CUDA(cudaFuncSetAttribute(k_floatSplit<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   const uint32_t tiles = p.tileEnd - p.tileBegin;
-  uint32_t ctas = min(tiles, (uint32_t)smCount() * (FT == kFtF64 ? 3u : 6u));
+  uint32_t perSm = FT == kFtF64 ? 3u : 6u;
+  if (const char* e = getenv("DGB_SPLIT_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
+  uint32_t ctas = min(tiles, (uint32_t)smCount() * perSm);
   p.tilesPerCta = divUp(tiles, ctas);
   ctas = divUp(tiles, p.tilesPerCta);
   {
