@@ -26,6 +26,56 @@
 
 namespace dietgpu {
 
+// ---- utils/DeviceUtils.h (the subset callers of the codec use: :17-23, :41-49, :61-67, :100, :111-119) ------
+#ifndef CUDA_VERIFY
+#define CUDA_VERIFY(X)                                                                              \
+  do {                                                                                              \
+    auto err__ = (X);                                                                               \
+    if (err__ != cudaSuccess)                                                                       \
+      throw std::runtime_error(std::string("CUDA error ") + cudaGetErrorName(err__) + " at " + __FILE__ + ":" + \
+                               std::to_string(__LINE__));                                           \
+  } while (0)
+#endif
+#ifndef CUDA_TEST_ERROR
+#define CUDA_TEST_ERROR() CUDA_VERIFY(cudaGetLastError())
+#endif
+
+inline int getCurrentDevice() {
+  int dev = -1;
+  CUDA_VERIFY(cudaGetDevice(&dev));
+  return dev;
+}
+inline void setCurrentDevice(int device) { CUDA_VERIFY(cudaSetDevice(device)); }
+inline int getNumDevices() {
+  int n = 0;
+  cudaError_t err = cudaGetDeviceCount(&n);
+  if (err == cudaErrorNoDevice) return 0;
+  CUDA_VERIFY(err);
+  return n;
+}
+inline int getDeviceForAddress(const void* p) {
+  if (!p) return -1;
+  cudaPointerAttributes att;
+  cudaError_t err = cudaPointerGetAttributes(&att, p);
+  if (err != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return att.type == cudaMemoryTypeDevice || att.type == cudaMemoryTypeManaged ? att.device : -1;
+}
+class DeviceScope {
+ public:
+  explicit DeviceScope(int device) : prev_(getCurrentDevice()) {
+    if (prev_ != device) setCurrentDevice(device);
+    else prev_ = -1;
+  }
+  ~DeviceScope() {
+    if (prev_ != -1) cudaSetDevice(prev_);
+  }
+ private:
+  int prev_;
+};
+
 // ---- utils/StackDeviceMemory.h --------------------------------------------------------------
 template <typename T>
 struct GpuMemoryReservation {
@@ -60,6 +110,9 @@ struct GpuMemoryReservation {
   cudaStream_t stream_ = nullptr;
   bool owned_ = false;
 };
+
+// All allocations are aligned to this boundary (utils/StackDeviceMemory.h:25-28)
+constexpr size_t kSDMAlignment = 256;
 
 class StackDeviceMemory {
  public:
