@@ -305,6 +305,7 @@ def main():
     alg = {  # algorithmic bytes per launch on this workload (DESIGN.md "Kernels")
         "k_floatSplit": U + N + N,      # read words; write raw section + exponent plane
         "k_encode": N + C_ans,          # read exponent plane; write ANS archives
+        "k_compressFused": U + N + C_ans,  # read words; write raw section + ANS payload (plane traffic is extra)
         "k_coalesce": 2 * C_ans,        # read block slots; write ANS payload (extra pass, not algorithmic)
         "k_decode": C_total + U,        # read archives; write words
     }

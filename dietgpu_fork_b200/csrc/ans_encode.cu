@@ -1,18 +1,18 @@
-// ANS encode side for sm_100a: byte histogram, probability normalisation, and the tile encoder
-// with single-pass (decoupled look-back) output compaction.
+// ANS encode side for sm_100a: byte histogram, checksum, probability normalisation, block encoder and
+// output compaction kernels plus their launchers. The device-side building blocks live in ans_encode.cuh.
 //
 // What is computed follows the reference (citations relative to /root/reference/):
 //   histogram            dietgpu/ans/GpuANSStatistics.cuh:21-143
 //   normalisation        dietgpu/ans/GpuANSStatistics.cuh:178-367
 //   per-warp rANS coder  dietgpu/ans/GpuANSEncode.cuh:49-211
 //   archive assembly     dietgpu/ans/GpuANSEncode.cuh:511-624
-// How it is computed does not: the reference encodes into an uncoalesced temp buffer, runs a
-// 1-3 kernel prefix sum and copies every compressed byte a second time. Here one persistent
-// kernel stages a tile of 8 blocks in shared memory, encodes it with 8 warps, obtains the tile's
-// output offset with a decoupled look-back over tile aggregates and writes states, block index
-// and payload straight to their final place; the last tile of an element writes the header.
+// How it is computed does not: the reference encodes into an uncoalesced temp buffer, runs a 1-3 kernel
+// prefix sum and copies every compressed byte a second time with one CTA per block; here warps encode
+// runs of blocks as one stream into L2-resident scratch slots and a single compaction kernel that already
+// knows every size writes payload, index, pdf and header.
 #include <cstdlib>
 
+#include "ans_encode.cuh"
 #include "internal.h"
 #include "prof.h"
 
@@ -185,356 +185,32 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
   return kOk;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Normalisation: counts -> pdf summing to 2^probBits, bit-exact with the reference
-// (dietgpu/ans/GpuANSStatistics.cuh:178-367). One 256-thread CTA per element; thread s owns
-// symbol s throughout. Instead of physically sorting we compute each symbol's rank in the
-// descending order of (q << 16 | s): the reference's "positions" are these ranks.
-//
-// Encode-table entry (ours, 8 bytes): x = magic m, y = (2^probBits - pdf) | shift << 12 | cdf' << 17,
-// such that for every state v the encoder can hold when it divides (v < pdf << (31 - probBits), i.e.
-// after renormalisation)
-//     floor(v / pdf) == umulhi(v, m) >> shift
-// and the update is v' = q * (2^probBits - pdf) + v + cdf'. For pdf >= 2: l = ceil(log2 pdf),
-// m = ceil(2^(31 + l) / pdf) <= 2^32 - 1 (2^31 for a power of two), shift = l - 1; the error term
-// e = m * pdf - 2^(31 + l) < pdf gives v * e < pdf^2 << (31 - probBits) <= 2^(31 + l), so the quotient
-// is exact. pdf == 1: m = 2^32 - 1 yields q = v - 1 (v >= 32 here), compensated by
-// cdf' = cdf + 2^probBits - 1; otherwise cdf' = cdf. Storing K - pdf in the low bits serves both the
-// renormalisation test (v >= pdf << (31 - probBits)  <=>  bit 31 of v + (y << (31 - probBits)), the
-// multiply drops every other field) and the update; cdf' sits in the high bits, where a single
-// shift-right-add (LEA.HI) extracts and adds it. Absent symbols (pdf 0) get an all-zero entry.
-// ---------------------------------------------------------------------------------------------
+// Normalisation kernel: one 256-thread CTA per element (see normalizeElement in ans_encode.cuh).
 __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elems,
                                                    const uint32_t* __restrict__ nDev,
                                                    const uint32_t* __restrict__ hist, int probBits,
                                                    uint2* __restrict__ table, uint32_t elemBegin) {
-  __shared__ uint32_t sKey[256];
-  __shared__ uint32_t sWarp[8];
-  const uint32_t e = elemBegin + blockIdx.x, s = threadIdx.x, lane = s & 31, w = s >> 5;
+  __shared__ uint32_t sm[256 + 16];
+  const uint32_t e = elemBegin + blockIdx.x;
   const uint32_t total = nDev ? nDev[e] : elems[e].n;
-  if (total == 0) { // reference leaves the table untouched (:192-195); we define it as zero
-    table[e * 256 + s] = make_uint2(0, 0);
-    return;
-  }
-  const uint32_t count = hist[e * 256 + s];
-  const uint32_t weight = 1u << probBits;
-  // :205-221 — fp32 divide (RN) then multiply (RN), truncation
-  float ratio = __fdiv_rn((float)count, (float)total);
-  uint32_t q = (uint32_t)__fmul_rn((float)weight, ratio);
-  if (count > 0 && q == 0) q = 1;
-
-  uint32_t ws = warpSum(q);
-  if (lane == 0) sWarp[w] = ws;
-  const uint32_t key = (q << 16) | s;
-  sKey[s] = key;
-  __syncthreads();
-  int sum = 0;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) sum += (int)sWarp[i];
-  // rank in descending key order == position after the reference's SortDescending (:229-252)
-  uint32_t pos = 0;
-#pragma unroll 16
-  for (int j = 0; j < 256; ++j) pos += (sKey[j] > key);
-
-  int diff = (int)weight - sum;
-  if (diff > 0) {
-    // :258-273 — the test is on the symbol id, not on the rank
-    while (diff > 0) {
-      int k = diff < 256 ? diff : 256;
-      if ((int)s < k) q += 1;
-      diff -= k;
-    }
-  } else if (diff < 0) {
-    // :274-315 — take one from the smallest entries that are still > 1, by position
-    diff = -diff;
-    while (diff > 0) {
-      int g = __syncthreads_count(q > 1);
-      int k = diff < g ? diff : g;
-      if (k <= 0) break;
-      if ((int)pos >= g - k && (int)pos < g) q -= 1;
-      diff -= k;
-    }
-  }
-  // exclusive scan over symbols -> cdf (:317-341)
-  uint32_t inc = q;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= (uint32_t)o) inc += t;
-  }
-  __syncthreads(); // sWarp reuse
-  if (lane == 31) sWarp[w] = inc;
-  __syncthreads();
-  uint32_t cdf = inc - q;
-  for (uint32_t i = 0; i < w; ++i) cdf += sWarp[i];
-
-  uint2 entry = make_uint2(0, 0);
-  if (q) {
-    const uint32_t l = 32 - __clz(q - 1); // q == 1 -> clz(0) == 32 -> 0
-    uint32_t m = 0xffffffffu, shift = 0, cdfAdj = cdf + weight - 1;
-    if (q > 1) {
-      m = (uint32_t)(((1ull << (31 + l)) + q - 1) / q);
-      shift = l - 1;
-      cdfAdj = cdf;
-    }
-    entry = make_uint2(m, (weight - q) | (shift << 12) | (cdfAdj << 17));
-  }
-  table[e * 256 + s] = entry;
+  normalizeElement<256>(hist + (size_t)e * 256, total, probBits, table + (size_t)e * 256, sm);
 }
 
-// ---------------------------------------------------------------------------------------------
-// Block encoder + compaction (two kernels).
-//
-// k_encode: one autonomous warp per 4096-symbol ANS block, no CTA-wide barrier, no waiting on
-// other warps, no shared-memory input staging.
-//   symbols: one byte load per lane and symbol row straight from global memory (a row is one
-//            32-byte sector, four rows share an L1 line), issued a whole 8-row batch ahead of use
-//   table:   the element's 4 KB encode table, read through L1, four rows ahead of use
-//   rows:    rANS step per 32 symbols (13 instructions), ballot/popc compaction into a 2.5 KB
-//            per-warp staging buffer
-//   flush:   the staged words go, as 16-byte vectors, to the block's slot of a scratch area when
-//            the block ends (typical data: once per block) or when the buffer could overflow
-//            within the next batch; final lane states go straight into the archive, the word
-//            count into a per-block size array
-// k_coalesce: every size is known when it starts; per tile of 8 blocks it sums the sizes before
-// the tile and copies the payload from the scratch slots (L2-resident: just written) to its final
-// place together with the block index, the pdf table and the header.
-//
-// Why not a single pass: a block's final offset is known only when ALL earlier blocks of the
-// element are encoded, i.e. after the slowest of them; measured on B200, warps spent as long
-// waiting on that look-back as encoding (profiles/r1_k_encode_v2), and holding a worst-case 5 KB
-// block in shared memory while waiting capped occupancy at 24 warps/SM.
-// ---------------------------------------------------------------------------------------------
-struct EncParams {
-  EncodeArgs a;
-  const uint2* table;   // [numElems][256]
-  uint8_t* scratch;     // [totalBlocks][kSlotBytes]
-  uint32_t* blockWords; // [totalBlocks] words emitted per block
-  uint32_t* groupWords; // [totalGroups] sum of roundUp(words, 8) per group of 256 blocks, zeroed
-  uint32_t* runCounter;  // zeroed; hands out runs beyond each warp's first one
-  uint32_t totalWarps;
-  uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
-};
-
-constexpr uint32_t kEncWarps = 4;
-constexpr uint32_t kEncCtasPerSm = 10;
-constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
-constexpr uint32_t kEncBatchRows = 8;
-constexpr uint32_t kRunBlocks = 4;              // consecutive blocks one warp encodes as one stream (half a tile)
-constexpr uint32_t kBlockBatches = kBlockSyms / (32 * kEncBatchRows);
-constexpr uint32_t kEncTableBytes = 256 * 8;     // per-warp copy of the element's encode table
-constexpr uint32_t kEncStageBytes = 2560;
-constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncBatchRows * 64; // room for one more batch, worst case
-constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
-constexpr uint32_t kEncWarpSmem = kEncTableBytes + kEncStageBytes;
-
-// One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
-// {m, (K - pdf) | shift << 12 | cdf' << 17}; outPtr = shared-memory byte address of the next free
-// staging word. Written in PTX to pin the instruction selection.
-template <int PB>
-__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      ".reg .b32 sum, vote, pre, addr, t, q, c, k;\n"
-      "mad.lo.u32 sum, %3, %5, %0;\n"          // ((K - pdf) << (31 - PB)) + state: bit 31 <=> renormalise
-      "setp.lt.s32 p, sum, 0;\n"
-      "vote.sync.ballot.b32 vote, p, 0xffffffff;\n"
-      "and.b32 pre, vote, %4;\n"
-      "popc.b32 pre, pre;\n"
-      "mad.lo.u32 addr, pre, 2, %1;\n"
-      "@p st.shared.u16 [addr], %0;\n"
-      "@p shr.u32 %0, %0, 16;\n"
-      "popc.b32 t, vote;\n"
-      "mad.lo.u32 %1, t, 2, %1;\n"
-      "mul.hi.u32 q, %0, %2;\n"
-      "shr.u32 c, %3, 12;\n"
-      "shf.r.wrap.b32 q, q, 0, c;\n"           // floor(state / pdf)
-      "and.b32 k, %3, 0xfff;\n"
-      "shr.u32 c, %3, 17;\n"
-      "add.u32 c, c, %0;\n"                    // state + cdf'
-      "mad.lo.u32 %0, q, k, c;\n"              // q * (K - pdf) + state + cdf'
-      "}\n"
-      : "+r"(state), "+r"(outPtr)
-      : "r"(e.x), "r"(e.y), "r"(ltMask), "n"(1u << (31 - PB))
-      : "memory");
-}
-
-// partial last row: lanes >= rem neither emit nor update (:94-136)
-template <int PB>
-__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask,
-                                               bool valid) {
-  const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
-  const uint32_t vote = __ballot_sync(0xffffffffu, wr);
-  if (wr) {
-    uint32_t addr = outPtr + 2u * __popc(vote & ltMask);
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "r"(state) : "memory");
-    state >>= 16;
-  }
-  outPtr += 2u * __popc(vote);
-  const uint32_t q = __funnelshift_r(__umulhi(state, e.x), 0u, e.y >> 12);
-  const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
-  state = valid ? ns : state;
-}
-
-__device__ __forceinline__ uint32_t ldSym(const uint8_t* p) {
-  uint32_t v;
-  asm volatile("ld.global.nc.L2::256B.u8 %0, [%1];" : "=r"(v) : "l"(p));
-  return v;
-}
-
-// table entry of symbol `sym` from the warp's shared-memory copy
-__device__ __forceinline__ uint2 ldEnt(uint32_t tabAddr, uint32_t sym) {
-  uint2 e;
-  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(tabAddr + sym * 8));
-  return e;
-}
-
+// Stand-alone block encoder (see encodeRun in ans_encode.cuh). A warp's first run is static, further
+// runs are handed out in order by an atomic counter (fetched one run ahead), so the resident warps
+// always stream one contiguous window of the input and finish together.
 template <int PB>
 __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
-  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  uint8_t* tabSmem = smem + w * kEncWarpSmem;
-  uint8_t* stage = tabSmem + kEncTableBytes;
-  const uint32_t tabAddr = smemAddr(tabSmem), stageAddr = smemAddr(stage);
-  const uint32_t ltMask = laneMaskLt();
-  const EncodeArgs& a = p.a;
-  uint32_t guess = 0;
-
-  // Work unit = run of kRunBlocks consecutive blocks of one element (half of an 8-block tile): one
-  // element lookup and one uninterrupted symbol stream per run. A warp's first run is static, further
-  // runs are handed out in order by an atomic counter (fetched one run ahead), so the resident warps
-  // always stream one contiguous window of the input and finish together.
-  uint32_t curElem = 0xffffffffu, n = 0, nb = 0, blockBase = 0, tileBase = 0, nextTileBase = 0;
-  uint32_t* groupSum = nullptr;
-  const uint8_t* elemSrc = nullptr;
-  uint8_t* ans = nullptr;
-  const uint32_t numRuns = (p.tileEnd - p.tileBegin) * (kTileBlocks / kRunBlocks);
-  uint32_t run = blockIdx.x * kEncWarps + w;
+  const uint32_t wi = threadIdx.x >> 5;
+  EncWarp w;
+  w.init(smem + wi * kEncWarpSmem);
+  const uint32_t numRuns = (p.tileEnd - p.tileBegin) * kRunsPerTile;
+  uint32_t run = blockIdx.x * kEncWarps + wi;
   while (run < numRuns) {
     uint32_t nextRun = 0;
-    if (lane == 0) nextRun = p.totalWarps + atomicAdd(p.runCounter, 1u);
-    const uint32_t tile = p.tileBegin + run / (kTileBlocks / kRunBlocks);
-    if (curElem == 0xffffffffu || tile >= nextTileBase || tile < tileBase) {
-      curElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, guess);
-      guess = curElem;
-      const Elem el = a.elems[curElem];
-      nextTileBase = a.elems[curElem + 1].tileBase;
-      tileBase = el.tileBase;
-      blockBase = el.blockBase;
-      groupSum = p.groupWords + el.groupBase;
-      elemSrc = (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + lane;
-      { // the element's 2 KB table -> this warp's shared-memory copy
-        const uint4* g = (const uint4*)(p.table + (size_t)curElem * 256);
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < 4; ++i) ((uint4*)tabSmem)[lane + 32 * i] = g[lane + 32 * i];
-        __syncwarp();
-      }
-      n = a.nDev ? a.nDev[curElem] : el.n;
-      nb = divUp(n, kBlockSyms);
-      ans = (uint8_t*)el.out;
-      if (a.floatType != kFtNone) {
-        const uint8_t* fbase = (const uint8_t*)el.out + el.sizeBias;
-        ans = (uint8_t*)fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
-        if (a.round) ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
-      }
-    }
-    uint32_t blk = (tile - tileBase) * kTileBlocks + (run % (kTileBlocks / kRunBlocks)) * kRunBlocks;
-    if (blk < nb) { // else: empty element, or the device-side size is smaller than the host bound
-      const uint32_t runSyms = min(n, (blk + kRunBlocks) * kBlockSyms) - blk * kBlockSyms;
-      const uint8_t* src = elemSrc + (size_t)blk * kBlockSyms;
-
-      uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
-      // staged words -> scratch slot of block `blk`. final: pad with zero words to a multiple of 8 words,
-      // publish the sizes and the lane states, reset for the next block; otherwise whole 16-byte vectors
-      // go out and the remainder moves to the front of the buffer
-      auto flush = [&](bool final) {
-        const uint32_t gb = blockBase + blk;
-        uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
-        uint32_t bytes = outPtr - stageAddr;
-        __syncwarp();
-        if (final) {
-          const uint32_t padded = roundUp(bytes, 16);
-          if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
-          __syncwarp();
-          if (lane == 0) {
-            p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
-            atomicAdd(&groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
-          }
-          bytes = padded;
-        }
-        const uint32_t nv = bytes >> 4;
-        for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
-        if (final) {
-          // final lane states go straight to their place in the archive (:584-589)
-          ((uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane] = state;
-          __syncwarp(); // the staging buffer is reused by the next block
-          state = kStateMin;
-          outPtr = stageAddr;
-          flushedVecs = 0;
-          ++blk;
-        } else {
-          const uint32_t remBytes = bytes & 15u;
-          uint32_t carry = 0;
-          if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
-          __syncwarp();
-          if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
-          __syncwarp();
-          flushedVecs += nv;
-          outPtr = stageAddr + remBytes;
-        }
-      };
-
-      const uint32_t rows = runSyms >> 5, rem = runSyms & 31u;
-      const uint32_t batches = rows / kEncBatchRows;
-      if (batches) {
-        // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
-        // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
-        // symbol of row r + 10. Symbols are thus requested 8 rows (>= 150 issue slots x resident warps)
-        // before the dependent table load, table entries 2 rows before their step. The stream runs
-        // through block boundaries; only the state and the staging buffer are reset there.
-        uint32_t sym[8];
-        uint2 ent[2];
-        ent[0] = ldEnt(tabAddr, ldSym(src));
-        ent[1] = ldEnt(tabAddr, ldSym(src + 32));
-#pragma unroll
-        for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
-        {
-          const uint8_t* ld = batches > 1 ? src + 8 * 32 : src;
-          sym[0] = ldSym(ld);
-          sym[1] = ldSym(ld + 32);
-        }
-        const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
-        for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
-          // rows past the end of the run are replaced by re-reads of its first rows (valid memory, the
-          // values are never used): the loads stay unconditional, so nothing waits on them here
-          const uint8_t* ld1 = b + 1 < batches ? nx : src;
-          const uint8_t* ld2 = b + 2 < batches ? nx : src;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            encStep<PB>(state, ent[i & 1], outPtr, ltMask);
-            ent[i & 1] = ldEnt(tabAddr, sym[(i + 2) & 7]);
-            sym[(i + 2) & 7] = ldSym((i < 6 ? ld1 : ld2) + i * 32);
-          }
-          if ((b & (kBlockBatches - 1)) == kBlockBatches - 1) flush(true);
-          else if (outPtr - stageAddr >= kEncFlushAt) flush(false);
-        }
-      }
-      // last block of an element: leftover rows and the partial row
-      if (rows % kEncBatchRows || rem) {
-        if (outPtr - stageAddr >= kEncFlushAt) flush(false);
-        const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
-        for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
-          encStep<PB>(state, ldEnt(tabAddr, ldSym(tail + r * 32)), outPtr, ltMask);
-        if (rem) {
-          const bool valid = lane < rem;
-          const uint32_t sym = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
-          encStepPartial<PB>(state, ldEnt(tabAddr, sym), outPtr, ltMask, valid);
-        }
-      }
-      if (runSyms & (kBlockSyms - 1)) flush(true); // the partial block
-    }
+    if (w.lane == 0) nextRun = p.totalWarps + atomicAdd(p.runCounter, 1u);
+    encodeRun<PB, false>(p, w, run);
     run = __shfl_sync(0xffffffffu, nextRun, 0);
   }
 }
@@ -628,12 +304,28 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
 int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s) {
   es.table = tmp.alloc<uint2>((size_t)a.numElems * 256);
   es.blockWords = tmp.alloc<uint32_t>(a.totalTiles);
-  es.groupWords = tmp.alloc<uint32_t>(totalGroups + a.numElems + 1); // + one run counter per possible launch
+  // one zeroed control array: group sums | run counters (one per possible launch) | fused-kernel control
+  const size_t ctrlWords = (size_t)totalGroups + a.numElems + 1 + kFusedCtrlFixed + 2 * (size_t)a.numElems;
+  es.groupWords = tmp.alloc<uint32_t>(ctrlWords);
   es.scratch = (uint8_t*)tmp.alloc((size_t)a.totalTiles * kSlotBytes);
   if (tmp.failed()) return kErrCuda;
   es.runCounters = es.groupWords + totalGroups;
-  DGB_CUDA(cudaMemsetAsync(es.groupWords, 0, (size_t)(totalGroups + a.numElems + 1) * 4, s));
+  es.fusedCtrl = es.runCounters + a.numElems + 1;
+  DGB_CUDA(cudaMemsetAsync(es.groupWords, 0, ctrlWords * 4, s));
   return kOk;
+}
+
+void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r) {
+  p.a = a;
+  p.table = es.table;
+  p.scratch = es.scratch;
+  p.blockWords = es.blockWords;
+  p.groupWords = es.groupWords;
+  p.runCounter = es.runCounters + r.e0;
+  p.ready = nullptr;
+  p.tileBegin = r.tile0;
+  p.tileEnd = r.tile1;
+  p.totalWarps = 0;
 }
 
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {
@@ -646,14 +338,7 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   DGB_CUDA(cudaGetLastError());
 
   EncParams p;
-  p.a = a;
-  p.table = es.table;
-  p.scratch = es.scratch;
-  p.blockWords = es.blockWords;
-  p.groupWords = es.groupWords;
-  p.runCounter = es.runCounters + r.e0;
-  p.tileBegin = r.tile0;
-  p.tileEnd = r.tile1;
+  fillEncParams(p, a, es, r);
   const uint32_t runs = (r.tile1 - r.tile0) * (kTileBlocks / kRunBlocks);
   uint32_t perSm = kEncCtasPerSm;
   if (const char* e = getenv("DGB_ENC_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
@@ -676,6 +361,13 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
     default: rc = launch(k_encode<11>); break;
   }
   if (rc) return rc;
+  return launchCoalesce(a, es, r, s);
+}
+
+int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {
+  if (r.tile1 <= r.tile0) return kOk;
+  EncParams p;
+  fillEncParams(p, a, es, r);
   {
     ProfScope ps__("k_coalesce", s);
     k_coalesce<<<r.tile1 - r.tile0, 256, 0, s>>>(p, a.probBits);

@@ -1,0 +1,422 @@
+// Device-side building blocks of the ANS encoder, shared by the stand-alone kernels (ans_encode.cu) and the
+// fused split + normalise + encode kernel (fused.cu): table normalisation, the rANS row step and the
+// warp-level "encode one run of blocks" routine.
+#pragma once
+#include "common.cuh"
+#include "internal.h"
+
+namespace dgb {
+
+// ---------------------------------------------------------------------------------------------
+// Normalisation: counts -> pdf summing to 2^probBits, bit-exact with the reference
+// (dietgpu/ans/GpuANSStatistics.cuh:178-367). One CTA of NT threads per element; thread t owns the
+// symbols t, t + NT, ... throughout. Instead of physically sorting we compute each symbol's rank in
+// the descending order of (q << 16 | s): the reference's "positions" are these ranks.
+//
+// Encode-table entry (ours, 8 bytes): x = magic m, y = (2^probBits - pdf) | shift << 12 | cdf' << 17,
+// such that for every state v the encoder can hold when it divides (v < pdf << (31 - probBits), i.e.
+// after renormalisation)
+//     floor(v / pdf) == umulhi(v, m) >> shift
+// and the update is v' = q * (2^probBits - pdf) + v + cdf'. For pdf >= 2: l = ceil(log2 pdf),
+// m = ceil(2^(31 + l) / pdf) <= 2^32 - 1 (2^31 for a power of two), shift = l - 1; the error term
+// e = m * pdf - 2^(31 + l) < pdf gives v * e < pdf^2 << (31 - probBits) <= 2^(31 + l), so the quotient
+// is exact. pdf == 1: m = 2^32 - 1 yields q = v - 1 (v >= 32 here), compensated by
+// cdf' = cdf + 2^probBits - 1; otherwise cdf' = cdf. Storing K - pdf in the low bits serves both the
+// renormalisation test (v >= pdf << (31 - probBits)  <=>  bit 31 of v + (y << (31 - probBits)), the
+// multiply drops every other field) and the update; cdf' sits in the high bits, where a single
+// shift-right-add (LEA.HI) extracts and adds it. Absent symbols (pdf 0) get an all-zero entry.
+//
+// sm: at least 256 + 16 words of shared memory. All NT threads of the CTA must call it.
+// ---------------------------------------------------------------------------------------------
+template <int NT>
+__device__ __forceinline__ uint32_t normBlockSum(uint32_t v, uint32_t* sRed, uint32_t lane, uint32_t w) {
+  constexpr int NW = NT / 32;
+  v = warpSum(v);
+  __syncthreads(); // previous readers of sRed are done
+  if (lane == 0) sRed[w] = v;
+  __syncthreads();
+  uint32_t sum = 0;
+#pragma unroll
+  for (int i = 0; i < NW; ++i) sum += sRed[i];
+  return sum;
+}
+
+template <int NT>
+__device__ void normalizeElement(const uint32_t* hist, uint32_t total, int probBits, uint2* table, uint32_t* sm) {
+  constexpr int S = 256 / NT;
+  constexpr int NW = NT / 32;
+  uint32_t* sKey = sm;
+  uint32_t* sRed = sm + 256;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (total == 0) { // reference leaves the table untouched (:192-195); we define it as zero
+#pragma unroll
+    for (int k = 0; k < S; ++k) table[tid + k * NT] = make_uint2(0, 0);
+    return;
+  }
+  const uint32_t weight = 1u << probBits;
+  uint32_t q[S], key[S], pos[S];
+  uint32_t mySum = 0;
+  __syncthreads(); // sm may still be in use by the caller
+#pragma unroll
+  for (int k = 0; k < S; ++k) {
+    const uint32_t s = tid + k * NT;
+    const uint32_t count = __ldcg(hist + s);
+    // :205-221 — fp32 divide (RN) then multiply (RN), truncation
+    const float ratio = __fdiv_rn((float)count, (float)total);
+    q[k] = (uint32_t)__fmul_rn((float)weight, ratio);
+    if (count > 0 && q[k] == 0) q[k] = 1;
+    key[k] = (q[k] << 16) | s;
+    sKey[s] = key[k];
+    mySum += q[k];
+  }
+  const int sum = (int)normBlockSum<NT>(mySum, sRed, lane, w); // also publishes sKey
+  // rank in descending key order == position after the reference's SortDescending (:229-252)
+#pragma unroll
+  for (int k = 0; k < S; ++k) {
+    uint32_t c = 0;
+#pragma unroll 16
+    for (int j = 0; j < 256; ++j) c += (sKey[j] > key[k]);
+    pos[k] = c;
+  }
+  int diff = (int)weight - sum;
+  if (diff > 0) {
+    // :258-273 — the test is on the symbol id, not on the rank
+    while (diff > 0) {
+      const int kk = diff < 256 ? diff : 256;
+#pragma unroll
+      for (int k = 0; k < S; ++k)
+        if ((int)(tid + k * NT) < kk) q[k] += 1;
+      diff -= kk;
+    }
+  } else if (diff < 0) {
+    // :274-315 — take one from the smallest entries that are still > 1, by position
+    diff = -diff;
+    while (diff > 0) {
+      uint32_t c = 0;
+#pragma unroll
+      for (int k = 0; k < S; ++k) c += q[k] > 1;
+      const int g = (int)normBlockSum<NT>(c, sRed, lane, w);
+      const int kk = diff < g ? diff : g;
+      if (kk <= 0) break;
+#pragma unroll
+      for (int k = 0; k < S; ++k)
+        if ((int)pos[k] >= g - kk && (int)pos[k] < g) q[k] -= 1;
+      diff -= kk;
+    }
+  }
+  // exclusive scan over symbols -> cdf (:317-341); symbols of group k precede those of group k + 1
+  uint32_t base = 0;
+#pragma unroll
+  for (int k = 0; k < S; ++k) {
+    uint32_t inc = q[k];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (uint32_t)o) inc += t;
+    }
+    __syncthreads(); // sRed reuse
+    if (lane == 31) sRed[w] = inc;
+    __syncthreads();
+    uint32_t cdf = base + inc - q[k];
+    uint32_t groupTotal = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+      const uint32_t x = sRed[i];
+      cdf += (uint32_t)i < w ? x : 0u;
+      groupTotal += x;
+    }
+    base += groupTotal;
+
+    uint2 entry = make_uint2(0, 0);
+    if (q[k]) {
+      const uint32_t l = 32 - __clz(q[k] - 1); // q == 1 -> clz(0) == 32 -> 0
+      uint32_t m = 0xffffffffu, shift = 0, cdfAdj = cdf + weight - 1;
+      if (q[k] > 1) {
+        m = (uint32_t)(((1ull << (31 + l)) + q[k] - 1) / q[k]);
+        shift = l - 1;
+        cdfAdj = cdf;
+      }
+      entry = make_uint2(m, (weight - q[k]) | (shift << 12) | (cdfAdj << 17));
+    }
+    table[tid + k * NT] = entry;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Block encoder.
+// ---------------------------------------------------------------------------------------------
+struct EncParams {
+  EncodeArgs a;
+  uint2* table;         // [numElems][256]
+  uint8_t* scratch;     // [totalBlocks][kSlotBytes]
+  uint32_t* blockWords; // [totalBlocks] words emitted per block
+  uint32_t* groupWords; // [totalGroups] sum of roundUp(words, 8) per group of 256 blocks, zeroed
+  uint32_t* runCounter; // zeroed; hands out runs beyond each warp's first one
+  uint32_t totalWarps;
+  uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
+  // fused kernel only: per-element flag, non-zero once the element's exponent plane and table are complete
+  const uint32_t* ready;
+};
+
+void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r);
+
+constexpr uint32_t kEncWarps = 4;
+constexpr uint32_t kEncCtasPerSm = 10;
+constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
+constexpr uint32_t kEncBatchRows = 8;
+constexpr uint32_t kRunBlocks = 4;               // consecutive blocks one warp encodes as one stream (half a tile)
+constexpr uint32_t kRunsPerTile = kTileBlocks / kRunBlocks;
+constexpr uint32_t kBlockBatches = kBlockSyms / (32 * kEncBatchRows);
+constexpr uint32_t kEncTableBytes = 256 * 8;     // per-warp copy of the element's encode table
+constexpr uint32_t kEncStageBytes = 2560;
+constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncBatchRows * 64; // room for one more batch, worst case
+constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
+constexpr uint32_t kEncWarpSmem = kEncTableBytes + kEncStageBytes;
+
+// One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
+// {m, (K - pdf) | shift << 12 | cdf' << 17}; outPtr = shared-memory byte address of the next free
+// staging word. Written in PTX to pin the instruction selection.
+template <int PB>
+__device__ __forceinline__ void encStep(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b32 sum, vote, pre, addr, t, q, c, k;\n"
+      "mad.lo.u32 sum, %3, %5, %0;\n"          // ((K - pdf) << (31 - PB)) + state: bit 31 <=> renormalise
+      "setp.lt.s32 p, sum, 0;\n"
+      "vote.sync.ballot.b32 vote, p, 0xffffffff;\n"
+      "and.b32 pre, vote, %4;\n"
+      "popc.b32 pre, pre;\n"
+      "mad.lo.u32 addr, pre, 2, %1;\n"
+      "@p st.shared.u16 [addr], %0;\n"
+      "@p shr.u32 %0, %0, 16;\n"
+      "popc.b32 t, vote;\n"
+      "mad.lo.u32 %1, t, 2, %1;\n"
+      "mul.hi.u32 q, %0, %2;\n"
+      "shr.u32 c, %3, 12;\n"
+      "shf.r.wrap.b32 q, q, 0, c;\n"           // floor(state / pdf)
+      "and.b32 k, %3, 0xfff;\n"
+      "shr.u32 c, %3, 17;\n"
+      "add.u32 c, c, %0;\n"                    // state + cdf'
+      "mad.lo.u32 %0, q, k, c;\n"              // q * (K - pdf) + state + cdf'
+      "}\n"
+      : "+r"(state), "+r"(outPtr)
+      : "r"(e.x), "r"(e.y), "r"(ltMask), "n"(1u << (31 - PB))
+      : "memory");
+}
+
+// partial last row: lanes >= rem neither emit nor update (:94-136)
+template <int PB>
+__device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_t& outPtr, uint32_t ltMask,
+                                               bool valid) {
+  const bool wr = valid && (int32_t)((e.y << (31 - PB)) + state) < 0;
+  const uint32_t vote = __ballot_sync(0xffffffffu, wr);
+  if (wr) {
+    uint32_t addr = outPtr + 2u * __popc(vote & ltMask);
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "r"(state) : "memory");
+    state >>= 16;
+  }
+  outPtr += 2u * __popc(vote);
+  const uint32_t q = __funnelshift_r(__umulhi(state, e.x), 0u, e.y >> 12);
+  const uint32_t ns = q * (e.y & 0xfffu) + state + (e.y >> 17);
+  state = valid ? ns : state;
+}
+
+// One symbol row = one 32-byte sector: nothing to reuse in L1, so the load goes to L2 (.cg), which also makes
+// it safe in the fused kernel where another SM wrote the plane moments ago; L2 fetches 256 B per miss.
+__device__ __forceinline__ uint32_t ldSym(const uint8_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.cg.L2::256B.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+// table entry of symbol `sym` from the warp's shared-memory copy
+__device__ __forceinline__ uint2 ldEnt(uint32_t tabAddr, uint32_t sym) {
+  uint2 e;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(tabAddr + sym * 8));
+  return e;
+}
+
+__device__ __forceinline__ uint32_t ldAcquire(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp-level encoder. Work unit = run of kRunBlocks consecutive blocks of one element (half of an
+// 8-block tile): one element lookup and one uninterrupted symbol stream per run.
+//   symbols: one byte load per lane and symbol row straight from global memory, requested 8 rows
+//            (one batch) before the dependent table load
+//   table:   the element's 2 KB encode table in a per-warp shared-memory copy, read 2 rows ahead
+//   rows:    rANS step per 32 symbols, ballot/popc compaction into a 2.5 KB per-warp staging buffer
+//   flush:   the staged words go, as 16-byte vectors, to the block's slot of a scratch area when the
+//            block ends (typical data: once per block) or when the buffer could overflow within the
+//            next batch; final lane states go straight into the archive, the word count into a
+//            per-block size array
+// ---------------------------------------------------------------------------------------------
+struct EncWarp {
+  uint8_t* tabSmem;
+  uint8_t* stage;
+  uint32_t tabAddr, stageAddr, ltMask, lane;
+  // element cache
+  uint32_t curElem, n, nb, blockBase, tileBase, nextTileBase, guess;
+  uint32_t* groupSum;
+  const uint8_t* elemSrc;
+  uint8_t* ans;
+
+  __device__ __forceinline__ void init(uint8_t* warpSmem) {
+    tabSmem = warpSmem;
+    stage = warpSmem + kEncTableBytes;
+    tabAddr = smemAddr(tabSmem);
+    stageAddr = smemAddr(stage);
+    ltMask = laneMaskLt();
+    lane = laneId();
+    curElem = 0xffffffffu;
+    n = nb = blockBase = tileBase = nextTileBase = guess = 0;
+    groupSum = nullptr;
+    elemSrc = nullptr;
+    ans = nullptr;
+  }
+};
+
+// FUSED: the element's plane and table are produced by other CTAs of the same launch; wait for its flag.
+template <int PB, bool FUSED>
+__device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32_t run) {
+  const EncodeArgs& a = p.a;
+  const uint32_t lane = w.lane;
+  uint8_t* const stage = w.stage;
+  const uint32_t stageAddr = w.stageAddr, tabAddr = w.tabAddr, ltMask = w.ltMask;
+  const uint32_t tile = p.tileBegin + run / kRunsPerTile;
+  if (w.curElem == 0xffffffffu || tile >= w.nextTileBase || tile < w.tileBase) {
+    w.curElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, w.guess);
+    w.guess = w.curElem;
+    const Elem el = a.elems[w.curElem];
+    w.nextTileBase = a.elems[w.curElem + 1].tileBase;
+    w.tileBase = el.tileBase;
+    w.blockBase = el.blockBase;
+    w.groupSum = p.groupWords + el.groupBase;
+    w.elemSrc = (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + lane;
+    if (FUSED) {
+      if (lane == 0) {
+        while (ldAcquire(p.ready + w.curElem) == 0) __nanosleep(100);
+      }
+      __syncwarp();
+    }
+    { // the element's 2 KB table -> this warp's shared-memory copy
+      const uint4* g = (const uint4*)(p.table + (size_t)w.curElem * 256);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ((uint4*)w.tabSmem)[lane + 32 * i] = __ldcg(g + lane + 32 * i);
+      __syncwarp();
+    }
+    w.n = a.nDev ? a.nDev[w.curElem] : el.n;
+    w.nb = divUp(w.n, kBlockSyms);
+    w.ans = (uint8_t*)el.out;
+    if (a.floatType != kFtNone) {
+      const uint8_t* fbase = (const uint8_t*)el.out + el.sizeBias;
+      w.ans = (uint8_t*)fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, w.n);
+      if (a.round) w.ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
+    }
+  }
+  uint32_t blk = (tile - w.tileBase) * kTileBlocks + (run % kRunsPerTile) * kRunBlocks;
+  if (blk >= w.nb) return; // empty element, or the device-side size is smaller than the host bound
+  const uint32_t n = w.n;
+  const uint32_t runSyms = min(n, (blk + kRunBlocks) * kBlockSyms) - blk * kBlockSyms;
+  const uint8_t* src = w.elemSrc + (size_t)blk * kBlockSyms;
+
+  uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;
+  // staged words -> scratch slot of block `blk`. final: pad with zero words to a multiple of 8 words,
+  // publish the sizes and the lane states, reset for the next block; otherwise whole 16-byte vectors
+  // go out and the remainder moves to the front of the buffer
+  auto flush = [&](bool final) {
+    const uint32_t gb = w.blockBase + blk;
+    uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
+    uint32_t bytes = outPtr - stageAddr;
+    __syncwarp();
+    if (final) {
+      const uint32_t padded = roundUp(bytes, 16);
+      if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
+      __syncwarp();
+      if (lane == 0) {
+        p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
+        atomicAdd(&w.groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
+      }
+      bytes = padded;
+    }
+    const uint32_t nv = bytes >> 4;
+    for (uint32_t i = lane; i < nv; i += 32) slot[flushedVecs + i] = ((const uint4*)stage)[i];
+    if (final) {
+      // final lane states go straight to their place in the archive (:584-589)
+      ((uint32_t*)(w.ans + kAnsFixedBytes))[blk * 32 + lane] = state;
+      __syncwarp(); // the staging buffer is reused by the next block
+      state = kStateMin;
+      outPtr = stageAddr;
+      flushedVecs = 0;
+      ++blk;
+    } else {
+      const uint32_t remBytes = bytes & 15u;
+      uint32_t carry = 0;
+      if (2 * lane < remBytes) carry = *(const uint16_t*)(stage + nv * 16 + 2 * lane);
+      __syncwarp();
+      if (2 * lane < remBytes) *(uint16_t*)(stage + 2 * lane) = (uint16_t)carry;
+      __syncwarp();
+      flushedVecs += nv;
+      outPtr = stageAddr + remBytes;
+    }
+  };
+
+  const uint32_t rows = runSyms >> 5, rem = runSyms & 31u;
+  const uint32_t batches = rows / kEncBatchRows;
+  if (batches) {
+    // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
+    // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
+    // symbol of row r + 10. Symbols are thus requested 8 rows (>= 150 issue slots x resident warps)
+    // before the dependent table load, table entries 2 rows before their step. The stream runs
+    // through block boundaries; only the state and the staging buffer are reset there.
+    uint32_t sym[8];
+    uint2 ent[2];
+    ent[0] = ldEnt(tabAddr, ldSym(src));
+    ent[1] = ldEnt(tabAddr, ldSym(src + 32));
+#pragma unroll
+    for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
+    {
+      const uint8_t* ld = batches > 1 ? src + 8 * 32 : src;
+      sym[0] = ldSym(ld);
+      sym[1] = ldSym(ld + 32);
+    }
+    const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
+    for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
+      // rows past the end of the run are replaced by re-reads of its first rows (valid memory, the
+      // values are never used): the loads stay unconditional, so nothing waits on them here
+      const uint8_t* ld1 = b + 1 < batches ? nx : src;
+      const uint8_t* ld2 = b + 2 < batches ? nx : src;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        encStep<PB>(state, ent[i & 1], outPtr, ltMask);
+        ent[i & 1] = ldEnt(tabAddr, sym[(i + 2) & 7]);
+        sym[(i + 2) & 7] = ldSym((i < 6 ? ld1 : ld2) + i * 32);
+      }
+      if ((b & (kBlockBatches - 1)) == kBlockBatches - 1) flush(true);
+      else if (outPtr - stageAddr >= kEncFlushAt) flush(false);
+    }
+  }
+  // last block of an element: leftover rows and the partial row
+  if (rows % kEncBatchRows || rem) {
+    if (outPtr - stageAddr >= kEncFlushAt) flush(false);
+    const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
+    for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
+      encStep<PB>(state, ldEnt(tabAddr, ldSym(tail + r * 32)), outPtr, ltMask);
+    if (rem) {
+      const bool valid = lane < rem;
+      const uint32_t sy = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
+      encStepPartial<PB>(state, ldEnt(tabAddr, sy), outPtr, ltMask, valid);
+    }
+  }
+  if (runSyms & (kBlockSyms - 1)) flush(true); // the partial block
+}
+
+} // namespace dgb

@@ -225,6 +225,16 @@ cudaStream_t sideStream() {
   return side[dev];
 }
 
+// DGB_FUSED=0 selects the separate split / normalise / encode launches (kept for the sparse and fp64 paths)
+bool fusedCompressEnabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("DGB_FUSED");
+    on = e ? (atoi(e) != 0) : 1;
+  }
+  return on != 0;
+}
+
 int overlapGroups() {
   static int g = -1;
   if (g < 0) {
@@ -299,6 +309,8 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);
+    if (planes == 1 && !nDev && !denseIn && fusedCompressEnabled())
+      return launchFusedFloatCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
     if ((rc = split(all, s))) return rc;
     for (int r = 0; r < planes; ++r)
       if ((rc = launchAnsEncode(args[r], es[r], all, s))) return rc;

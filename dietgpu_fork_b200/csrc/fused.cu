@@ -1,0 +1,183 @@
+// Fused float compress for sm_100a: float split, table normalisation and rANS block encoding of the exponent
+// plane in ONE persistent launch (then k_coalesce).
+//
+// Why: measured on B200 the split is bound by shared-memory atomic throughput and the
+// encoder by instruction issue; run back to back they add up, run on the same SMs at the same time they
+// overlap. Stream-level overlap of separate launches does not work (the grids take turns); so the roles live in
+// one grid:
+//   * every CTA draws a per-SM ticket; the first `splitCtasPerSm` CTAs of each SM take the split role, the rest
+//     the encode role, so every SM runs both kinds of work side by side;
+//   * split CTAs claim 32768-word tiles in order from an atomic counter (element-major, so elements complete
+//     one after the other), write raw bytes into the archive and exponent bytes into the plane, and add their
+//     histogram to the element's global bins; the CTA that completes an element's last tile normalises its
+//     table and publishes the element's ready flag (release);
+//   * encode warps claim runs of 4 blocks in the same order, wait (acquire) for the run's element, and encode
+//     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
+//   * a split CTA that finds no tile left becomes an encode CTA.
+// Split CTAs never wait, so the flags always arrive; the grid is sized to be co-resident.
+#include <cstdlib>
+
+#include "ans_encode.cuh"
+#include "float_split.cuh"
+#include "internal.h"
+#include "prof.h"
+
+namespace dgb {
+
+struct FusedParams {
+  SplitParams sp;
+  EncParams ep;
+  uint32_t* splitCounter; // zeroed
+  uint32_t* smTicket;     // [512] zeroed
+  uint32_t* tilesDone;    // [numElems] zeroed
+  uint32_t* ready;        // [numElems] zeroed
+  uint32_t totalTiles;
+  uint32_t splitCtasPerSm;
+};
+
+constexpr uint32_t kFusedThreads = kEncWarps * 32; // 128
+constexpr uint32_t kFusedHistBytes = splitHistWords<kFusedThreads>() * 4;
+constexpr uint32_t kFusedNormBytes = (256 + 16) * 4;
+constexpr uint32_t kFusedSmem =
+    kEncWarps * kEncWarpSmem > kFusedHistBytes + kFusedNormBytes ? kEncWarps * kEncWarpSmem : kFusedHistBytes + kFusedNormBytes;
+
+template <int FT, int PB>
+__global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(const FusedParams p) {
+  static_assert(FloatTraits<FT>::kPlanes == 1, "single exponent plane only");
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint32_t sBcast[2];
+  const uint32_t tid = threadIdx.x;
+
+  if (tid == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    sBcast[0] = atomicAdd(&p.smTicket[smid & 511u], 1u) < p.splitCtasPerSm ? 1u : 0u;
+  }
+  __syncthreads();
+  const bool splitRole = sBcast[0] != 0;
+  __syncthreads();
+
+  if (splitRole) {
+    uint32_t* sh = (uint32_t*)smem;
+    uint32_t* normSm = (uint32_t*)(smem + kFusedHistBytes);
+    for (uint32_t i = tid; i < kFusedHistBytes / 4; i += kFusedThreads) sh[i] = 0;
+    uint32_t guess = 0;
+    for (;;) {
+      if (tid == 0) sBcast[0] = atomicAdd(p.splitCounter, 1u);
+      __syncthreads();
+      const uint32_t tile = sBcast[0];
+      if (tile >= p.totalTiles) break;
+      const uint32_t e = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tile, guess);
+      guess = e;
+      const Elem el = p.sp.elems[e];
+      const uint32_t n = el.n;
+      splitTile<FT, kFusedThreads>(p.sp, e, el, n, tile, sh);
+      __syncthreads();
+      splitHistFlush<kFusedThreads>(sh, p.sp.hist0 + (size_t)e * 256, tid);
+      __threadfence(); // plane, raw bytes and histogram of this tile before the tile count
+      __syncthreads();
+      if (tid == 0) {
+        const uint32_t done = atomicAdd(&p.tilesDone[e], 1u) + 1u;
+        sBcast[1] = done == p.sp.elems[e + 1].tileBase - el.tileBase ? 1u : 0u;
+      }
+      __syncthreads();
+      if (sBcast[1]) { // this CTA completed the element: its histogram is final
+        __threadfence();
+        normalizeElement<kFusedThreads>(p.sp.hist0 + (size_t)e * 256, n, PB, p.ep.table + (size_t)e * 256, normSm);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) stRelease(p.ready + e, 1u);
+      }
+      // sBcast[0] is rewritten only after the next barrier-separated iteration start
+      __syncthreads();
+    }
+    __syncthreads();
+  }
+
+  // ---- encode role ----
+  EncWarp w;
+  w.init(smem + (tid >> 5) * kEncWarpSmem);
+  const uint32_t numRuns = p.totalTiles * kRunsPerTile;
+  uint32_t run = 0;
+  if (w.lane == 0) run = atomicAdd(p.ep.runCounter, 1u);
+  run = __shfl_sync(0xffffffffu, run, 0);
+  while (run < numRuns) {
+    uint32_t nextRun = 0;
+    if (w.lane == 0) nextRun = atomicAdd(p.ep.runCounter, 1u);
+    encodeRun<PB, true>(p.ep, w, run);
+    run = __shfl_sync(0xffffffffu, nextRun, 0);
+  }
+}
+
+template <int FT, int PB>
+static int launchFusedT(FusedParams& p, cudaStream_t s) {
+  auto kern = k_compressFused<FT, PB>;
+  DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmem));
+  int perSm = 0;
+  DGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, (int)kFusedThreads, kFusedSmem));
+  if (perSm < 2) return kErrInternal;
+  if (perSm > (int)kEncCtasPerSm) perSm = (int)kEncCtasPerSm;
+  uint32_t splitPerSm = 3;
+  if (const char* e = getenv("DGB_FUSED_SPLIT_CTAS")) splitPerSm = (uint32_t)atoi(e); // experiment knob
+  if (splitPerSm < 1) splitPerSm = 1;
+  if (splitPerSm >= (uint32_t)perSm) splitPerSm = (uint32_t)perSm - 1;
+  p.splitCtasPerSm = splitPerSm;
+  // enough CTAs for the work, never more than fit at once (encode warps wait on split CTAs)
+  const uint32_t want = divUp(p.totalTiles * kRunsPerTile, kEncWarps) + p.totalTiles;
+  const uint32_t grid = min(want, (uint32_t)smCount() * (uint32_t)perSm);
+  {
+    ProfScope ps__("k_compressFused", s);
+    kern<<<grid, kFusedThreads, kFusedSmem, s>>>(p);
+  }
+  DGB_CUDA(cudaGetLastError());
+  return kOk;
+}
+
+template <int FT>
+static int launchFusedPb(FusedParams& p, int pb, cudaStream_t s) {
+  switch (pb) {
+    case 9: return launchFusedT<FT, 9>(p, s);
+    case 10: return launchFusedT<FT, 10>(p, s);
+    default: return launchFusedT<FT, 11>(p, s);
+  }
+}
+
+int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
+                             const uint32_t* checksum, int useChecksum, cudaStream_t s) {
+  if (a.numElems == 0) return kOk;
+  if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
+  if (a.nDev || ft == kFtF64) return kErrInvalidArg;
+  const WorkRange all{0, a.numElems, 0, totalTiles, 0, a.totalTiles};
+  FusedParams p;
+  fillEncParams(p.ep, a, es, all);
+  p.sp.elems = a.elems;
+  p.sp.numElems = a.numElems;
+  p.sp.tileBegin = 0;
+  p.sp.tileEnd = totalTiles;
+  p.sp.tilesPerCta = 1;
+  p.sp.nDev = nullptr;
+  p.sp.denseIn = nullptr;
+  p.sp.plane0 = (uint8_t*)a.planeBase;
+  p.sp.plane1 = nullptr;
+  p.sp.hist0 = (uint32_t*)a.hist;
+  p.sp.hist1 = nullptr;
+  p.sp.checksum = checksum;
+  p.sp.useChecksum = useChecksum;
+  p.splitCounter = es.fusedCtrl;
+  p.smTicket = es.fusedCtrl + 1;
+  p.tilesDone = es.fusedCtrl + kFusedCtrlFixed;
+  p.ready = p.tilesDone + a.numElems;
+  p.ep.ready = p.ready;
+  p.totalTiles = totalTiles;
+  int rc;
+  switch (ft) {
+    case kFtF16: rc = launchFusedPb<kFtF16>(p, a.probBits, s); break;
+    case kFtBF16: rc = launchFusedPb<kFtBF16>(p, a.probBits, s); break;
+    case kFtF32: rc = launchFusedPb<kFtF32>(p, a.probBits, s); break;
+    default: return kErrInvalidArg;
+  }
+  if (rc) return rc;
+  return launchCoalesce(a, es, all, s);
+}
+
+} // namespace dgb

@@ -131,6 +131,8 @@ struct EncodeArgs {
 };
 // Enqueues normalise + encode for one exponent plane / byte stream. Scratch comes from `tmp`.
 // A slice of the work list: elements [e0, e1) with their 8-block tiles and 4096-symbol blocks.
+constexpr uint32_t kFusedCtrlFixed = 1 + 512; // split tile counter + per-SM role tickets
+
 struct WorkRange {
   uint32_t e0, e1, tile0, tile1, blk0, blk1;
 };
@@ -140,12 +142,19 @@ struct EncodeScratch {
   uint32_t* blockWords;
   uint32_t* groupWords;
   uint32_t* runCounters;
+  uint32_t* fusedCtrl; // [kFusedCtrlFixed + 2 * numElems]: split counter, SM tickets | tilesDone | ready
   uint8_t* scratch;
 };
 // totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
 int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s);
 // Enqueues normalise + encode + compaction for the elements of `r` on stream s.
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
+// compaction only (k_coalesce), for callers that produced the block slots themselves
+int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
+// float split + table normalisation + block encoding of one exponent plane in ONE persistent launch, then
+// k_coalesce. Single-plane float types, host-known sizes, dense input (fused.cu).
+int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
+                             const uint32_t* checksum, int useChecksum, cudaStream_t s);
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or
 // output (useOut = 1); n = nDev[e] when given, else Elem::n. maxUnits bounds n.

@@ -1,0 +1,10 @@
+#!/bin/bash
+# parity first (bounded: a deadlock must not hang the box), then the fused kernel at several role splits
+timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+run() { echo "fused=$1 split_ctas=$2"; DGB_FUSED=$1 DGB_FUSED_SPLIT_CTAS=$2 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['phases']['compress_GBps_uncompressed'], d['phases']['kernels_ms_per_step'])"; }
+run 0 0
+run 1 1
+run 1 2
+run 1 3
+run 1 4
+run 1 5
