@@ -163,15 +163,17 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
 constexpr uint32_t kEncWarps = 4;
 constexpr uint32_t kEncCtasPerSm = 10;
 constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
-constexpr uint32_t kEncBatchRows = 8;
+constexpr uint32_t kEncChunkRows = 16;            // rows per staged symbol chunk (512 symbols, one 16-byte load per lane)
+constexpr uint32_t kEncChunk = kEncChunkRows * 32;
 constexpr uint32_t kRunBlocks = 4;               // consecutive blocks one warp encodes as one stream (half a tile)
 constexpr uint32_t kRunsPerTile = kTileBlocks / kRunBlocks;
-constexpr uint32_t kBlockBatches = kBlockSyms / (32 * kEncBatchRows);
+constexpr uint32_t kBlockChunks = kBlockSyms / kEncChunk;
 constexpr uint32_t kEncTableBytes = 256 * 8;     // per-warp copy of the element's encode table
-constexpr uint32_t kEncStageBytes = 2560;
-constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncBatchRows * 64; // room for one more batch, worst case
+constexpr uint32_t kEncStageBytes = 2304;
+constexpr uint32_t kEncFlushAt = kEncStageBytes - kEncChunkRows * 64; // room for one more chunk, worst case
+constexpr uint32_t kEncRingBytes = 2 * kEncChunk; // double-buffered symbol chunks
 constexpr uint32_t kSlotBytes = kStageWords * 2; // scratch bytes per block (worst case, probBits 11)
-constexpr uint32_t kEncWarpSmem = kEncTableBytes + kEncStageBytes;
+constexpr uint32_t kEncWarpSmem = kEncTableBytes + kEncStageBytes + kEncRingBytes;
 
 // One rANS step for 32 symbols (dietgpu/ans/GpuANSEncode.cuh:49-90). e = table entry
 // {m, (K - pdf) | shift << 12 | cdf' << 17}; outPtr = shared-memory byte address of the next free
@@ -222,11 +224,32 @@ __device__ __forceinline__ void encStepPartial(uint32_t& state, uint2 e, uint32_
   state = valid ? ns : state;
 }
 
-// One symbol row = one 32-byte sector: nothing to reuse in L1, so the load goes to L2 (.cg), which also makes
-// it safe in the fused kernel where another SM wrote the plane moments ago; L2 fetches 256 B per miss.
-__device__ __forceinline__ uint32_t ldSym(const uint8_t* p) {
+// 16 bytes of symbols per lane = one 512-symbol chunk per warp. The data is used once: the load bypasses L1
+// (.cg), which also makes it safe in the fused kernel where another SM wrote the plane moments ago.
+__device__ __forceinline__ uint4 ldChunkVec(const uint8_t* p) {
+  uint4 v;
+  asm volatile("ld.global.cg.L2::256B.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ldSymByte(const uint8_t* p) {
   uint32_t v;
-  asm volatile("ld.global.cg.L2::256B.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+// Lane's 16 bytes [16 * lane, 16 * lane + 16) of the chunk starting at `base` (chunk-relative validity:
+// `avail` bytes). Fast path: aligned and fully inside; otherwise byte loads, zero beyond the end.
+__device__ __forceinline__ uint4 ldChunk(const uint8_t* base, uint32_t avail, uint32_t lane, bool aligned) {
+  const uint8_t* q = base + lane * 16;
+  if (aligned && lane * 16 + 16 <= avail) return ldChunkVec(q);
+  uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int k = 0; k < 16; ++k)
+    if (lane * 16 + k < avail) w[k >> 2] |= ldSymByte(q + k) << (8 * (k & 3));
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ uint32_t ldsSym(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
 
@@ -261,7 +284,7 @@ __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
 struct EncWarp {
   uint8_t* tabSmem;
   uint8_t* stage;
-  uint32_t tabAddr, stageAddr, ltMask, lane;
+  uint32_t tabAddr, stageAddr, ringAddr, ltMask, lane;
   // element cache
   uint32_t curElem, n, nb, blockBase, tileBase, nextTileBase, guess;
   uint32_t* groupSum;
@@ -273,6 +296,7 @@ struct EncWarp {
     stage = warpSmem + kEncTableBytes;
     tabAddr = smemAddr(tabSmem);
     stageAddr = smemAddr(stage);
+    ringAddr = smemAddr(warpSmem + kEncTableBytes + kEncStageBytes);
     ltMask = laneMaskLt();
     lane = laneId();
     curElem = 0xffffffffu;
@@ -299,7 +323,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     w.tileBase = el.tileBase;
     w.blockBase = el.blockBase;
     w.groupSum = p.groupWords + el.groupBase;
-    w.elemSrc = (a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in) + lane;
+    w.elemSrc = a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in;
     if (FUSED) {
       if (lane == 0) {
         while (ldAcquire(p.ready + w.curElem) == 0) __nanosleep(100);
@@ -369,51 +393,53 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     }
   };
 
-  const uint32_t rows = runSyms >> 5, rem = runSyms & 31u;
-  const uint32_t batches = rows / kEncBatchRows;
-  if (batches) {
-    // software pipeline over rows: at row r the step consumes ent[r % 2]; that register then takes the
-    // table entry of row r + 2, whose symbol sits in sym[(r + 2) % 8]; that register in turn takes the
-    // symbol of row r + 10. Symbols are thus requested 8 rows (>= 150 issue slots x resident warps)
-    // before the dependent table load, table entries 2 rows before their step. The stream runs
-    // through block boundaries; only the state and the staging buffer are reset there.
-    uint32_t sym[8];
-    uint2 ent[2];
-    ent[0] = ldEnt(tabAddr, ldSym(src));
-    ent[1] = ldEnt(tabAddr, ldSym(src + 32));
-#pragma unroll
-    for (int r = 2; r < 8; ++r) sym[r] = ldSym(src + r * 32);
-    {
-      const uint8_t* ld = batches > 1 ? src + 8 * 32 : src;
-      sym[0] = ldSym(ld);
-      sym[1] = ldSym(ld + 32);
+  // Symbols: 512-symbol chunks, one 16-byte global load per lane, requested two chunks ahead of use and parked
+  // in a register; at the start of chunk c the data of chunk c + 1 goes into the other half of a 1 KB
+  // per-warp ring, so the row loop only sees shared-memory loads: symbol bytes 4 rows ahead, table entries
+  // 2 rows ahead of their step. The stream runs through block boundaries; only the state and the staging
+  // buffer are reset there.
+  const bool aligned = (((uintptr_t)src) & 15u) == 0;
+  const uint32_t numChunks = divUp(runSyms, kEncChunk);
+  const uint32_t ringAddr = w.ringAddr;
+  uint4 x = ldChunk(src, runSyms, lane, aligned);
+  __syncwarp(); // ring free (previous run)
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(ringAddr + lane * 16), "r"(x.x), "r"(x.y), "r"(x.z), "r"(x.w) : "memory");
+  if (numChunks > 1) x = ldChunk(src + kEncChunk, runSyms - kEncChunk, lane, aligned);
+  for (uint32_t c = 0; c < numChunks; ++c) {
+    const uint32_t cur = ringAddr + (c & 1u) * kEncChunk + lane;
+    const uint32_t nxt = ringAddr + ((c & 1u) ^ 1u) * kEncChunk + lane;
+    __syncwarp(); // every lane is done with the rows of chunk c - 1 (the half being overwritten)
+    if (c + 1 < numChunks) {
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(nxt - lane + lane * 16), "r"(x.x), "r"(x.y), "r"(x.z), "r"(x.w) : "memory");
+      if (c + 2 < numChunks) x = ldChunk(src + (size_t)(c + 2) * kEncChunk, runSyms - (c + 2) * kEncChunk, lane, aligned);
     }
-    const uint8_t* nx = src + 10 * 32; // row r + 10 for r = first row of the batch
-    for (uint32_t b = 0; b < batches; ++b, nx += kEncBatchRows * 32) {
-      // rows past the end of the run are replaced by re-reads of its first rows (valid memory, the
-      // values are never used): the loads stay unconditional, so nothing waits on them here
-      const uint8_t* ld1 = b + 1 < batches ? nx : src;
-      const uint8_t* ld2 = b + 2 < batches ? nx : src;
+    __syncwarp();
+    const uint32_t len = min(kEncChunk, runSyms - c * kEncChunk);
+    if (len == kEncChunk) {
+      uint32_t sym[4];
+      uint2 ent[2];
+      ent[0] = ldEnt(tabAddr, ldsSym(cur));
+      ent[1] = ldEnt(tabAddr, ldsSym(cur + 32));
+      sym[2] = ldsSym(cur + 64);
+      sym[3] = ldsSym(cur + 96);
+      sym[0] = ldsSym(cur + 128);
+      sym[1] = ldsSym(cur + 160);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        encStep<PB>(state, ent[i & 1], outPtr, ltMask);
-        ent[i & 1] = ldEnt(tabAddr, sym[(i + 2) & 7]);
-        sym[(i + 2) & 7] = ldSym((i < 6 ? ld1 : ld2) + i * 32);
+      for (int r = 0; r < 16; ++r) {
+        encStep<PB>(state, ent[r & 1], outPtr, ltMask);
+        if (r + 2 < 16) ent[r & 1] = ldEnt(tabAddr, sym[(r + 2) & 3]);
+        if (r + 6 < 16) sym[(r + 2) & 3] = ldsSym(cur + (r + 6) * 32);
       }
-      if ((b & (kBlockBatches - 1)) == kBlockBatches - 1) flush(true);
+      if ((c & (kBlockChunks - 1)) == kBlockChunks - 1) flush(true);
       else if (outPtr - stageAddr >= kEncFlushAt) flush(false);
-    }
-  }
-  // last block of an element: leftover rows and the partial row
-  if (rows % kEncBatchRows || rem) {
-    if (outPtr - stageAddr >= kEncFlushAt) flush(false);
-    const uint8_t* tail = src + (size_t)batches * (kEncBatchRows * 32);
-    for (uint32_t r = 0; r < rows % kEncBatchRows; ++r)
-      encStep<PB>(state, ldEnt(tabAddr, ldSym(tail + r * 32)), outPtr, ltMask);
-    if (rem) {
-      const bool valid = lane < rem;
-      const uint32_t sy = valid ? ldSym(tail + (rows % kEncBatchRows) * 32) : 0u;
-      encStepPartial<PB>(state, ldEnt(tabAddr, sy), outPtr, ltMask, valid);
+    } else { // last chunk of an element: leftover rows and the partial row
+      const uint32_t rows = len >> 5, rem = len & 31u;
+      for (uint32_t r = 0; r < rows; ++r) encStep<PB>(state, ldEnt(tabAddr, ldsSym(cur + r * 32)), outPtr, ltMask);
+      if (rem) {
+        const bool valid = lane < rem;
+        const uint32_t sy = valid ? ldsSym(cur + rows * 32) : 0u;
+        encStepPartial<PB>(state, ldEnt(tabAddr, sy), outPtr, ltMask, valid);
+      }
     }
   }
   if (runSyms & (kBlockSyms - 1)) flush(true); // the partial block

@@ -111,16 +111,27 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     const uint32_t ng = len / G;
     const uint32_t g0 = off / G;
     const uint4* v = (const uint4*)in + g0;
+    // two vectors per thread and step, the next pair requested before the current one is processed
     uint32_t i = tid;
-    for (; i + 3 * NT < ng; i += 4 * NT) {
-      uint4 x[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) x[k] = v[i + NT * k];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
+    if (i + NT < ng) {
+      uint4 x0 = v[i], x1 = v[i + NT];
+      for (;;) {
+        const uint32_t j = i + 2 * NT;
+        const bool more = j + NT < ng;
+        uint4 y0, y1;
+        if (more) {
+          y0 = v[j];
+          y1 = v[j + NT];
+        }
         uint32_t ex[2], ex1[2];
-        splitGroup<FT>(x[k], g0 + i + NT * k, plane0, plane1, rs, ex, ex1);
+        splitGroup<FT>(x0, g0 + i, plane0, plane1, rs, ex, ex1);
         splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+        splitGroup<FT>(x1, g0 + i + NT, plane0, plane1, rs, ex, ex1);
+        splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+        i = j;
+        if (!more) break;
+        x0 = y0;
+        x1 = y1;
       }
     }
     for (; i < ng; i += NT) {
