@@ -265,6 +265,11 @@ __device__ __forceinline__ uint32_t ldAcquire(const uint32_t* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ uint32_t ldRelaxed(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -325,8 +330,13 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     w.groupSum = p.groupWords + el.groupBase;
     w.elemSrc = a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in;
     if (FUSED) {
-      if (lane == 0) {
-        while (ldAcquire(p.ready + w.curElem) == 0) __nanosleep(100);
+      if (lane == 0) { // relaxed polling with growing back-off (an acquire load per poll would flush L1 each time)
+        uint32_t ns = 200;
+        while (ldRelaxed(p.ready + w.curElem) == 0) {
+          __nanosleep(ns);
+          if (ns < 3200) ns *= 2;
+        }
+        (void)ldAcquire(p.ready + w.curElem);
       }
       __syncwarp();
     }

@@ -14,6 +14,7 @@
 namespace dgb {
 
 constexpr int kSplitRep = 4;
+constexpr uint32_t kSplitPrefetchVecs = 2048; // 32 KB ahead of the loads
 template <int NT> __host__ __device__ constexpr uint32_t splitHistWords() { return (NT / 32) * 256 * kSplitRep; } // per plane
 
 struct SplitParams {
@@ -115,9 +116,16 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     uint32_t i = tid;
     if (i + NT < ng) {
       uint4 x0 = v[i], x1 = v[i + NT];
+      // input ahead of the register pipeline is pulled into L2 (one request per lane = 512 B per warp): with
+      // two 16-byte loads per thread in flight, DRAM latency would otherwise cap the read rate
+      const uint4* vEnd = (const uint4*)in + (n * sizeof(Word)) / 16;
       for (;;) {
         const uint32_t j = i + 2 * NT;
         const bool more = j + NT < ng;
+        if (v + j + kSplitPrefetchVecs < vEnd) {
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(v + j + kSplitPrefetchVecs));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(v + j + NT + kSplitPrefetchVecs));
+        }
         uint4 y0, y1;
         if (more) {
           y0 = v[j];
