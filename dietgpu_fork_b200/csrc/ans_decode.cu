@@ -127,11 +127,15 @@ constexpr uint32_t kPieceWords = 512;                 // 1 KB
 constexpr uint32_t kDecRingBytes = 2 * kPieceWords * 2; // 2 pieces
 constexpr uint32_t kDecChunk = 512;                   // symbols per transposer buffer (16 rows)
 
+// Shared memory of a CTA, from a base aligned to the LUT size (so that "(x & mask) | base" forms both the
+// LUT and the ring addresses in one LOP3):
+//   LUT[planes] (4 << PB each) | ring[warps][planes] (2 KB each) | transposer[warps][planes] (2 x 512 B) |
+//   mbarriers[warps][planes] (2 x 8 B)
 template <int PLANES> __host__ __device__ constexpr uint32_t decWarpSmem() {
   return PLANES * (kDecRingBytes + 2 * kDecChunk + 16);
 }
 template <int PB, int PLANES> __host__ __device__ constexpr uint32_t decCtaSmem() {
-  return PLANES * (4u << PB) + kDecWarps * decWarpSmem<PLANES>();
+  return (4u << PB) /* alignment slack */ + PLANES * (4u << PB) + kDecWarps * decWarpSmem<PLANES>();
 }
 
 // per-plane decode context of one warp
@@ -158,18 +162,57 @@ __device__ __forceinline__ void decRequest(DecCtx& c, int upTo, uint32_t lane) {
   }
 }
 
+// One decode step of a full symbol row (dietgpu/ans/GpuANSDecode.cuh:55-90, :174-217): LUT lookup, state
+// update, ballot of the lanes that must renormalise, their 16-bit reads from the end of the block's words in
+// descending lane order. lutAddr is aligned to the LUT size and ringAddr to the ring size. Returns the LUT
+// entry (symbol in the low byte). PTX to pin the instruction selection (18 instructions).
 template <int PB>
-__device__ __forceinline__ uint32_t decStep(uint32_t& state, const DecCtx& c, uint32_t& ptrBytes,
-                                            uint32_t geMask, bool valid) {
+__device__ __forceinline__ uint32_t decStep(uint32_t& state, uint32_t lutAddr, uint32_t ringAddr, uint32_t& ptrBytes,
+                                            uint32_t geMask) {
   uint32_t e;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(c.lutAddr + ((state & ((1u << PB) - 1u)) << 2)));
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b32 a, hi, t, b, ns, v, pre, ra, w, c;\n"
+      "shl.b32 a, %0, 2;\n"
+      "lop3.b32 a, a, %6, %3, 0xEA;\n"        // ((state << 2) & mask) | lutAddr
+      "ld.shared.u32 %2, [a];\n"
+      "shr.u32 hi, %0, %7;\n"
+      "shr.u32 t, %2, 8;\n"
+      "and.b32 t, t, 0xfff;\n"                // pdf
+      "shr.u32 b, %2, 20;\n"                  // slot - cdf
+      "mad.lo.u32 ns, t, hi, b;\n"
+      "setp.lt.u32 p, ns, 32768;\n"
+      "vote.sync.ballot.b32 v, p, 0xffffffff;\n"
+      "and.b32 pre, v, %5;\n"
+      "popc.b32 pre, pre;\n"
+      "mad.lo.u32 ra, pre, 0xfffffffe, %1;\n" // ptr - 2 * (readers at or above this lane)
+      "lop3.b32 ra, ra, %8, %4, 0xEA;\n"      // (ra & ringMask) | ringAddr
+      "ld.shared.u16 w, [ra];\n"              // every lane loads (a valid ring slot); only readers use it
+      "@p prmt.b32 ns, w, ns, 0x5410;\n"      // (ns << 16) | w
+      "popc.b32 c, v;\n"
+      "mad.lo.u32 %1, c, 0xfffffffe, %1;\n"
+      "mov.b32 %0, ns;\n"
+      "}\n"
+      : "+r"(state), "+r"(ptrBytes), "=&r"(e)
+      : "r"(lutAddr), "r"(ringAddr), "r"(geMask), "n"(((1u << PB) - 1u) << 2), "n"(PB), "n"(kDecRingBytes - 1)
+      : "memory");
+  return e;
+}
+
+// partial row: lanes >= rem keep their state and read nothing
+template <int PB>
+__device__ __forceinline__ uint32_t decStepPartial(uint32_t& state, uint32_t lutAddr, uint32_t ringAddr,
+                                                   uint32_t& ptrBytes, uint32_t geMask, bool valid) {
+  uint32_t e;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(lutAddr + ((state & ((1u << PB) - 1u)) << 2)));
   uint32_t ns = ((e >> 8) & 0xfffu) * (state >> PB) + (e >> 20);
   ns = valid ? ns : state;
   const bool rd = valid && ns < kStateMin;
   const uint32_t vote = __ballot_sync(0xffffffffu, rd);
   if (rd) {
     uint32_t w;
-    const uint32_t a = c.ringAddr + ((ptrBytes - 2u * __popc(vote & geMask)) & (kDecRingBytes - 1));
+    const uint32_t a = ringAddr + ((ptrBytes - 2u * __popc(vote & geMask)) & (kDecRingBytes - 1));
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(w) : "r"(a));
     ns = (ns << 16) | w;
   }
@@ -208,19 +251,23 @@ template <int PB, int FT>
 __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode(const DecParams p) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t kLut = 1u << PB;
-  extern __shared__ __align__(128) uint8_t smem[];
-  uint32_t* sLut = (uint32_t*)smem; // kPlanes * kLut
+  extern __shared__ __align__(128) uint8_t smemRaw[];
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  uint8_t* ws = smem + kPlanes * kLut * 4 + w * decWarpSmem<kPlanes>();
-  // per plane: ring | transposer[2] | 2 mbarriers
+  // base aligned to the LUT size (see decCtaSmem)
+  const uint32_t rawAddr = smemAddr(smemRaw);
+  uint8_t* smem = smemRaw + (((rawAddr + kLut * 4 - 1) & ~(kLut * 4 - 1)) - rawAddr);
+  uint32_t* sLut = (uint32_t*)smem; // kPlanes * kLut
+  uint8_t* rings = smem + kPlanes * kLut * 4;
+  uint8_t* transBase = rings + kDecWarps * kPlanes * kDecRingBytes;
+  uint8_t* bars = transBase + kDecWarps * kPlanes * 2 * kDecChunk;
   uint8_t* trans[kPlanes];
   DecCtx ctx[kPlanes];
 #pragma unroll
   for (int pl = 0; pl < kPlanes; ++pl) {
-    uint8_t* base = ws + pl * (kDecRingBytes + 2 * kDecChunk + 16);
-    ctx[pl].ringAddr = smemAddr(base);
-    trans[pl] = base + kDecRingBytes;
-    ctx[pl].bar0 = smemAddr(base + kDecRingBytes + 2 * kDecChunk);
+    const uint32_t slot = w * kPlanes + pl;
+    ctx[pl].ringAddr = smemAddr(rings + slot * kDecRingBytes);
+    trans[pl] = transBase + slot * 2 * kDecChunk;
+    ctx[pl].bar0 = smemAddr(bars + slot * 16);
     ctx[pl].lutAddr = smemAddr(sLut + pl * kLut);
     if (lane == 0) {
       mbarInit(ctx[pl].bar0, 1);
@@ -300,18 +347,18 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
         const uint32_t symAddr = smemAddr(trans[pl] + buf * kDecChunk) + lane;
         if (rem) {
           const bool valid = lane < rem;
-          const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, valid);
+          const uint32_t ev = decStepPartial<PB>(state, cx.lutAddr, cx.ringAddr, ptrBytes, geMask, valid);
           if (valid) asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + rows * 32), "r"(ev) : "memory");
         }
         if (rows == 16) {
 #pragma unroll
           for (int r = 15; r >= 0; --r) {
-            const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, true);
+            const uint32_t ev = decStep<PB>(state, cx.lutAddr, cx.ringAddr, ptrBytes, geMask);
             asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + r * 32), "r"(ev) : "memory");
           }
         } else {
           for (int r = (int)rows - 1; r >= 0; --r) {
-            const uint32_t ev = decStep<PB>(state, cx, ptrBytes, geMask, true);
+            const uint32_t ev = decStep<PB>(state, cx.lutAddr, cx.ringAddr, ptrBytes, geMask);
             asm volatile("st.shared.u8 [%0], %1;" ::"r"(symAddr + r * 32), "r"(ev) : "memory");
           }
         }
