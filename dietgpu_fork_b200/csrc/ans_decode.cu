@@ -129,13 +129,17 @@ constexpr uint32_t kDecChunk = 512;                   // symbols per transposer 
 
 // Shared memory of a CTA, from a base aligned to the LUT size (so that "(x & mask) | base" forms both the
 // LUT and the ring addresses in one LOP3):
-//   LUT[planes] (4 << PB each) | ring[warps][planes] (2 KB each) | transposer[warps][planes] (2 x 512 B) |
-//   mbarriers[warps][planes] (2 x 8 B)
-template <int PLANES> __host__ __device__ constexpr uint32_t decWarpSmem() {
-  return PLANES * (kDecRingBytes + 2 * kDecChunk + 16);
+//   LUT[planes] (4 << PB each) | ring[warps][planes] (2 KB each) | transposer[warps][planes] (512 B) |
+//   raw stage[warps] | mbarriers[warps][planes] (2 x 8 B)
+// raw-section bytes of one 512-word chunk staged per warp by cp.async (single-plane float types)
+template <int FT> __host__ __device__ constexpr uint32_t decRawStage() {
+  return (FT == kFtF16 || FT == kFtBF16) ? kDecChunk : (FT == kFtF32 ? 3 * kDecChunk : 0);
 }
-template <int PB, int PLANES> __host__ __device__ constexpr uint32_t decCtaSmem() {
-  return (4u << PB) /* alignment slack */ + PLANES * (4u << PB) + kDecWarps * decWarpSmem<PLANES>();
+template <int FT> __host__ __device__ constexpr uint32_t decWarpSmem() {
+  return (FT == kFtF64 ? 2 : 1) * (kDecRingBytes + kDecChunk + 16) + decRawStage<FT>();
+}
+template <int PB, int FT> __host__ __device__ constexpr uint32_t decCtaSmem() {
+  return (4u << PB) /* alignment slack */ + (FT == kFtF64 ? 2 : 1) * (4u << PB) + kDecWarps * decWarpSmem<FT>();
 }
 
 // per-plane decode context of one warp
@@ -221,8 +225,52 @@ __device__ __forceinline__ uint32_t decStepPartial(uint32_t& state, uint32_t lut
   return e;
 }
 
+// Pulls the raw-section bytes of one block (the ones writeChunk will join with the block's symbols) into L2
+// when the block starts: one 128-byte line per lane and request, so the joins later wait an L2 hit instead of
+// a DRAM round trip.
 template <int FT>
-__device__ __forceinline__ void writeChunk(const DecInfo& d, uint8_t* outBase, uint32_t wordOff, uint32_t len,
+__device__ __forceinline__ void prefetchRawBlock(const DecInfo& d, uint32_t blk, uint32_t blkLen, uint32_t lane) {
+  if constexpr (FT != kFtNone) {
+    const RawSections rs = rawSections(FT, (uint8_t*)d.fbase + kFloatHeaderBytes, d.n);
+    constexpr uint32_t aBytes = FT == kFtF64 ? 4 : (FT == kFtF32 ? 2 : 1); // per word in section a
+    constexpr uint32_t bBytes = FT == kFtF64 ? 2 : (FT == kFtF32 ? 1 : 0);
+    const uint8_t* pa = (const uint8_t*)rs.a + (size_t)blk * kBlockSyms * aBytes;
+    for (uint32_t off = lane * 128; off < blkLen * aBytes; off += 32 * 128)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + off));
+    if constexpr (bBytes != 0) {
+      const uint8_t* pb = (const uint8_t*)rs.b + (size_t)blk * kBlockSyms * bBytes;
+      for (uint32_t off = lane * 128; off < blkLen * bBytes; off += 32 * 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + off));
+    }
+  }
+}
+
+// Starts the asynchronous copy of the chunk's raw bytes into the warp's stage (16 bytes per lane and request)
+// and returns raw-section pointers biased so that the global indices used by the join land in the stage.
+template <int FT>
+__device__ __forceinline__ RawSections stageRaw(const RawSections& g, uint32_t wordOff, uint32_t len, uint8_t* stage,
+                                                uint32_t lane) {
+  constexpr uint32_t aBytes = FT == kFtF32 ? 2 : 1;
+  const uint32_t stageAddr = smemAddr(stage);
+  const uint8_t* srcA = g.a + (size_t)wordOff * aBytes;
+  for (uint32_t off = lane * 16; off < len * aBytes; off += 512)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(stageAddr + off), "l"(srcA + off) : "memory");
+  RawSections r;
+  r.a = stage - (size_t)wordOff * aBytes;
+  r.b = r.a;
+  if constexpr (FT == kFtF32) {
+    const uint8_t* srcB = g.b + wordOff;
+    for (uint32_t off = lane * 16; off < len; off += 512)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(stageAddr + 2 * kDecChunk + off), "l"(srcB + off)
+                   : "memory");
+    r.b = stage + 2 * kDecChunk - wordOff;
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  return r;
+}
+
+template <int FT>
+__device__ __forceinline__ void writeChunk(const RawSections& rs, uint8_t* outBase, uint32_t wordOff, uint32_t len,
                                            const uint8_t* sym0, const uint8_t* sym1, uint32_t lane) {
   if constexpr (FT == kFtNone) {
     uint8_t* out = outBase + wordOff;
@@ -233,7 +281,6 @@ __device__ __forceinline__ void writeChunk(const DecInfo& d, uint8_t* outBase, u
     }
   } else {
     constexpr uint32_t G = FloatTraits<FT>::kGroup;
-    const RawSections rs = rawSections(FT, (uint8_t*)d.fbase + kFloatHeaderBytes, d.n);
     uint32_t vecWords = 0;
     if ((((uintptr_t)outBase) & 15u) == 0) {
       const uint32_t ng = len / G, g0 = wordOff / G;
@@ -259,14 +306,15 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
   uint32_t* sLut = (uint32_t*)smem; // kPlanes * kLut
   uint8_t* rings = smem + kPlanes * kLut * 4;
   uint8_t* transBase = rings + kDecWarps * kPlanes * kDecRingBytes;
-  uint8_t* bars = transBase + kDecWarps * kPlanes * 2 * kDecChunk;
+  uint8_t* rawStage = transBase + kDecWarps * kPlanes * kDecChunk + w * decRawStage<FT>();
+  uint8_t* bars = transBase + kDecWarps * kPlanes * kDecChunk + kDecWarps * decRawStage<FT>();
   uint8_t* trans[kPlanes];
   DecCtx ctx[kPlanes];
 #pragma unroll
   for (int pl = 0; pl < kPlanes; ++pl) {
     const uint32_t slot = w * kPlanes + pl;
     ctx[pl].ringAddr = smemAddr(rings + slot * kDecRingBytes);
-    trans[pl] = transBase + slot * 2 * kDecChunk;
+    trans[pl] = transBase + slot * kDecChunk;
     ctx[pl].bar0 = smemAddr(bars + slot * 16);
     ctx[pl].lutAddr = smemAddr(sLut + pl * kLut);
     if (lane == 0) {
@@ -326,11 +374,24 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
       outBase = a.denseBase ? a.denseBase + el.planeOff * sizeof(typename FloatTraits<FT == kFtNone ? kFtF16 : FT>::Word)
                             : (uint8_t*)el.out;
 
+    RawSections rsGlobal;
+    rsGlobal.a = rsGlobal.b = nullptr;
+    bool rawAligned = false;
+    if constexpr (FT != kFtNone) {
+      rsGlobal = rawSections(FT, (uint8_t*)d0.fbase + kFloatHeaderBytes, d0.n);
+      rawAligned = (((uintptr_t)d0.fbase) & 15u) == 0;
+      if (!rawAligned || decRawStage<FT>() == 0) prefetchRawBlock<FT>(d0, blk, blkLen, lane);
+    }
     const uint32_t numChunks = divUp(blkLen, kDecChunk);
     for (int c = (int)numChunks - 1; c >= 0; --c) {
       const uint32_t len = min(kDecChunk, blkLen - (uint32_t)c * kDecChunk);
       const uint32_t rows = len >> 5, rem = len & 31u;
-      const uint32_t buf = (uint32_t)c & 1u;
+      const uint32_t wordOff = FT == kFtNone ? (uint32_t)c * kDecChunk : blk * kBlockSyms + (uint32_t)c * kDecChunk;
+      // raw bytes of this chunk: asynchronous copy into the warp's stage while the chunk is decoded
+      RawSections rs = rsGlobal;
+      if constexpr (decRawStage<FT>() != 0) {
+        if (rawAligned) rs = stageRaw<FT>(rsGlobal, wordOff, len, rawStage, lane);
+      }
 #pragma unroll
       for (int pl = 0; pl < kPlanes; ++pl) {
         DecCtx& cx = ctx[pl];
@@ -344,7 +405,7 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
           phaseBits ^= 1u << (2 * pl + slot);
         }
         uint32_t state = cx.state, ptrBytes = cx.ptrBytes;
-        const uint32_t symAddr = smemAddr(trans[pl] + buf * kDecChunk) + lane;
+        const uint32_t symAddr = smemAddr(trans[pl]) + lane;
         if (rem) {
           const bool valid = lane < rem;
           const uint32_t ev = decStepPartial<PB>(state, cx.lutAddr, cx.ringAddr, ptrBytes, geMask, valid);
@@ -371,10 +432,10 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
           decRequest(cx, nq - 1, lane);
         }
       }
+      if constexpr (decRawStage<FT>() != 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncwarp();
-      const uint32_t wordOff = FT == kFtNone ? (uint32_t)c * kDecChunk : blk * kBlockSyms + (uint32_t)c * kDecChunk;
-      writeChunk<FT>(d0, outBase, wordOff, len, trans[0] + buf * kDecChunk, trans[kPlanes - 1] + buf * kDecChunk,
-                     lane);
+      writeChunk<FT>(rs, outBase, wordOff, len, trans[0], trans[kPlanes - 1], lane);
+      __syncwarp(); // transposer and raw stage are reused by the next chunk
     }
   }
 }
@@ -382,7 +443,7 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
 template <int PB, int FT>
 static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
-  constexpr uint32_t smemBytes = decCtaSmem<PB, kPlanes>();
+  constexpr uint32_t smemBytes = decCtaSmem<PB, FT>();
   DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   const uint32_t perSm = FT == kFtF64 ? 3u : 6u;
   uint32_t ctas = min(p.a.totalTiles, (uint32_t)smCount() * perSm);
