@@ -193,18 +193,19 @@ def main():
     rank = env_int("RANK", 0)
     local_rank = env_int("LOCAL_RANK", 0)
 
-    if args.impl == "reference" and world > 1 and rank != 0:
-        return 0  # rank 0 alone runs the reference arm
+    ref = RefLib() if args.impl == "reference" else None
+    if args.impl == "reference" and not ref.ok() and world > 1 and rank != 0:
+        return 0  # CPU stand-in (reference build absent): rank 0 alone runs it
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
     torch.cuda.set_device(local_rank)
     dist = None
-    if world > 1 and args.impl == "ours":
+    if world > 1 and (args.impl == "ours" or ref.ok()):
+        # the reference's CUDA build shards the batch exactly like ours: one rank per GPU for both arms
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    ref = RefLib() if args.impl == "reference" else None
     if args.impl == "reference" and not ref.ok():
         return reference_cpu_arm(args)
 

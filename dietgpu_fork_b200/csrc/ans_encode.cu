@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const 
   const uint32_t wi = threadIdx.x >> 5;
   EncWarp w;
   w.init(smem + wi * kEncWarpSmem);
-  const uint32_t numRuns = (p.tileEnd - p.tileBegin) * kRunsPerTile;
+  const uint32_t numRuns = (p.tileEnd - p.tileBegin) << p.runShift;
   uint32_t run = blockIdx.x * kEncWarps + wi;
   while (run < numRuns) {
     uint32_t nextRun = 0;
@@ -326,6 +326,7 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
   p.tileBegin = r.tile0;
   p.tileEnd = r.tile1;
   p.totalWarps = 0;
+  p.runShift = 1;
 }
 
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {
@@ -339,7 +340,8 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
 
   EncParams p;
   fillEncParams(p, a, es, r);
-  const uint32_t runs = (r.tile1 - r.tile0) * (kTileBlocks / kRunBlocks);
+  p.runShift = chooseRunShift(r.tile1 - r.tile0, (uint32_t)smCount() * kEncCtasPerSm * kEncWarps);
+  const uint32_t runs = (r.tile1 - r.tile0) << p.runShift;
   uint32_t perSm = kEncCtasPerSm;
   if (const char* e = getenv("DGB_ENC_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
   const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * perSm);

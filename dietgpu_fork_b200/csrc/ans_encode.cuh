@@ -154,6 +154,7 @@ struct EncParams {
   uint32_t* runCounter; // zeroed; hands out runs beyond each warp's first one
   uint32_t totalWarps;
   uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
+  uint32_t runShift;           // log2(runs per tile): runs are 8 >> runShift consecutive blocks (4 for large batches)
   // fused kernel only: per-element flag, non-zero once the element's exponent plane and table are complete
   const uint32_t* ready;
 };
@@ -165,8 +166,13 @@ constexpr uint32_t kEncCtasPerSm = 10;
 constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
 constexpr uint32_t kEncChunkRows = 16;            // rows per staged symbol chunk (512 symbols, one 16-byte load per lane)
 constexpr uint32_t kEncChunk = kEncChunkRows * 32;
-constexpr uint32_t kRunBlocks = 4;               // consecutive blocks one warp encodes as one stream (half a tile)
-constexpr uint32_t kRunsPerTile = kTileBlocks / kRunBlocks;
+// Run = consecutive blocks one warp encodes as one stream: 4 (half a tile) when there is enough work to fill the
+// GPU with such runs, 2 or 1 for small batches.
+inline uint32_t chooseRunShift(uint32_t totalTiles, uint32_t warpsWanted) {
+  uint32_t shift = 1;
+  while (shift < 3 && (totalTiles << shift) < warpsWanted) ++shift;
+  return shift;
+}
 constexpr uint32_t kBlockChunks = kBlockSyms / kEncChunk;
 constexpr uint32_t kEncTableBytes = 256 * 8;     // per-warp copy of the element's encode table
 constexpr uint32_t kEncStageBytes = 2304;
@@ -275,8 +281,8 @@ __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Warp-level encoder. Work unit = run of kRunBlocks consecutive blocks of one element (half of an
-// 8-block tile): one element lookup and one uninterrupted symbol stream per run.
+// Warp-level encoder. Work unit = run of 8 >> runShift consecutive blocks of one element (half of an
+// 8-block tile for large batches): one element lookup and one uninterrupted symbol stream per run.
 //   symbols: one byte load per lane and symbol row straight from global memory, requested 8 rows
 //            (one batch) before the dependent table load
 //   table:   the element's 2 KB encode table in a per-warp shared-memory copy, read 2 rows ahead
@@ -319,7 +325,8 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
   const uint32_t lane = w.lane;
   uint8_t* const stage = w.stage;
   const uint32_t stageAddr = w.stageAddr, tabAddr = w.tabAddr, ltMask = w.ltMask;
-  const uint32_t tile = p.tileBegin + run / kRunsPerTile;
+  const uint32_t runBlocks = kTileBlocks >> p.runShift;
+  const uint32_t tile = p.tileBegin + (run >> p.runShift);
   if (w.curElem == 0xffffffffu || tile >= w.nextTileBase || tile < w.tileBase) {
     w.curElem = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, w.guess);
     w.guess = w.curElem;
@@ -356,10 +363,10 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
       if (a.round) w.ans += *(const uint32_t*)(fbase + 16); // firstCompSegmentBytes
     }
   }
-  uint32_t blk = (tile - w.tileBase) * kTileBlocks + (run % kRunsPerTile) * kRunBlocks;
+  uint32_t blk = (tile - w.tileBase) * kTileBlocks + (run & ((1u << p.runShift) - 1u)) * runBlocks;
   if (blk >= w.nb) return; // empty element, or the device-side size is smaller than the host bound
   const uint32_t n = w.n;
-  const uint32_t runSyms = min(n, (blk + kRunBlocks) * kBlockSyms) - blk * kBlockSyms;
+  const uint32_t runSyms = min(n, (blk + runBlocks) * kBlockSyms) - blk * kBlockSyms;
   const uint8_t* src = w.elemSrc + (size_t)blk * kBlockSyms;
 
   uint32_t state = kStateMin, outPtr = stageAddr, flushedVecs = 0;

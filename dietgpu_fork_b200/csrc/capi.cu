@@ -226,6 +226,8 @@ cudaStream_t sideStream() {
 }
 
 // DGB_FUSED=0 selects the separate split / normalise / encode launches (kept for the sparse and fp64 paths)
+constexpr uint32_t kFusedMinElems = 1;
+
 bool fusedCompressEnabled() {
   static int on = -1;
   if (on < 0) {
@@ -309,7 +311,7 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);
-    if (planes == 1 && !nDev && !denseIn && fusedCompressEnabled())
+    if (planes == 1 && !nDev && !denseIn && num >= kFusedMinElems && fusedCompressEnabled())
       return launchFusedFloatCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
     if ((rc = split(all, s))) return rc;
     for (int r = 0; r < planes; ++r)

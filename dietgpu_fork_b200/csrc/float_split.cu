@@ -8,7 +8,7 @@
 
 namespace dgb {
 
-template <int FT>
+template <int FT, bool PIPE>
 __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
   constexpr int kPlanes = FloatTraits<FT>::kPlanes;
   constexpr uint32_t kHistWords = splitHistWords<256>();
@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
     }
     const Elem el = p.elems[e];
     const uint32_t n = p.nDev ? p.nDev[e] : el.n;
-    splitTile<FT, 256>(p, e, el, n, tile, sh);
+    splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh);
   }
   if (cur != 0xffffffffu) {
     __syncthreads();
@@ -45,7 +45,9 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
 template <int FT>
 static int launchSplitT(SplitParams& p, cudaStream_t s) {
   constexpr uint32_t smemBytes = FloatTraits<FT>::kPlanes * splitHistWords<256>() * 4;
-  DGB_CUDA(cudaFuncSetAttribute(k_floatSplit<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  static const bool pipe = getenv("DGB_SPLIT_PIPE") ? atoi(getenv("DGB_SPLIT_PIPE")) != 0 : true; // experiment knob
+  auto kern = pipe ? k_floatSplit<FT, true> : k_floatSplit<FT, false>;
+  DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   const uint32_t tiles = p.tileEnd - p.tileBegin;
   uint32_t perSm = FT == kFtF64 ? 3u : 6u;
   if (const char* e = getenv("DGB_SPLIT_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
@@ -54,7 +56,7 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
   ctas = divUp(tiles, p.tilesPerCta);
   {
     ProfScope ps__("k_floatSplit", s);
-    k_floatSplit<FT><<<ctas, 256, smemBytes, s>>>(p);
+    kern<<<ctas, 256, smemBytes, s>>>(p);
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;

@@ -79,7 +79,7 @@ __device__ __forceinline__ void splitHistGroup(uint32_t* wh0, uint32_t* wh1, con
 
 // One tile of element e (el = elems[e], n = its word count) by the NT threads of the CTA. sh: the CTA's
 // histogram bins (kPlanes * splitHistWords<NT>() words, zeroed by the caller).
-template <int FT, int NT>
+template <int FT, int NT, bool PIPE = true>
 __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, const Elem& el, uint32_t n, uint32_t tile,
                                           uint32_t* sh) {
   using Tr = FloatTraits<FT>;
@@ -112,9 +112,22 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     const uint32_t ng = len / G;
     const uint32_t g0 = off / G;
     const uint4* v = (const uint4*)in + g0;
-    // two vectors per thread and step, the next pair requested before the current one is processed
     uint32_t i = tid;
-    if (i + NT < ng) {
+    if constexpr (!PIPE) { // four independent vectors per thread and step
+      for (; i + 3 * NT < ng; i += 4 * NT) {
+        uint4 x[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) x[k] = v[i + NT * k];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint32_t ex[2], ex1[2];
+          splitGroup<FT>(x[k], g0 + i + NT * k, plane0, plane1, rs, ex, ex1);
+          splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+        }
+      }
+    }
+    // two vectors per thread and step, the next pair requested before the current one is processed
+    if (PIPE && i + NT < ng) {
       uint4 x0 = v[i], x1 = v[i + NT];
       // input ahead of the register pipeline is pulled into L2 (one request per lane = 512 B per warp): with
       // two 16-byte loads per thread in flight, DRAM latency would otherwise cap the read rate

@@ -1,0 +1,188 @@
+"""Device-resident throughput of every BASELINE.json config, ours next to the reference's CUDA build (when
+oracle/_ref/libdietgpu_ref.so exists) with the identical harness: same buffers, CUDA events on the current stream,
+3 warm-ups, N timed calls, compressed outputs compared byte-count for byte-count. One JSON line per config.
+Usage: python scripts/bench_configs.py [--steps 10] [--only ans,bf16,f32_1g,f32_64,f16,f64,sparse]"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from dietgpu_fork_b200 import _capi, codec  # noqa: E402
+
+REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libdietgpu_ref.so")
+REF = C.CDLL(REF_PATH) if os.path.exists(REF_PATH) else None
+PEAK = 6545.9
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+
+
+def pa(ts):
+    return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+
+
+def u32(v):
+    return (C.c_uint32 * len(v))(*v)
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def timed(fn, steps, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / steps
+
+
+def run_config(name, kind, ft, ins, counts, steps, sparse=False):
+    """kind: 'ans' (bytes) or 'float'. ins: device tensors; counts: bytes (ans) or words (float)."""
+    n = len(ins)
+    wb = 1 if kind == "ans" else codec.WORD_BYTES[ft]
+    U = sum(counts) * wb
+    if kind == "ans":
+        mx = max(codec.get_max_compressed_size(c) for c in counts)
+    elif sparse:
+        mx = max(codec.get_max_sparse_float_compressed_size(ft, c) for c in counts)
+    else:
+        mx = max(codec.get_max_float_compressed_size(ft, c) for c in counts)
+    mx = (mx + 15) // 16 * 16
+    comp = torch.zeros((n, mx), dtype=torch.uint8, device="cuda")
+    rows = [comp[i] for i in range(n)]
+    sizes = torch.zeros(n, dtype=torch.int32, device="cuda")
+    outs = [torch.empty(c * wb, dtype=torch.uint8, device="cuda") for c in counts]
+    ok = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    dsz = torch.zeros(n, dtype=torch.int32, device="cuda")
+    temp = torch.empty(int(2.5 * U) + (64 << 20), dtype=torch.uint8, device="cuda")
+    res = {"config": name, "batch": n, "uncompressed_bytes": U}
+
+    def ours_c():
+        if kind == "ans":
+            codec.ans_encode_batch_pointer(ins, rows, sizes, 10, False, temp=temp, in_sizes=list(counts))
+        elif sparse:
+            codec.float_compress_sparse(ft, ins, rows, sizes, 10, temp=temp, in_sizes=list(counts))
+        else:
+            codec.float_compress(ft, ins, rows, sizes, 10, False, temp=temp, in_sizes=list(counts))
+
+    def ours_d():
+        if kind == "ans":
+            codec.ans_decode_batch_pointer(rows, outs, ok, dsz, 10, False, temp=temp, out_capacity=list(counts))
+        elif sparse:
+            codec.float_decompress_sparse(ft, rows, outs, ok, dsz, 10, temp=temp, out_capacity=list(counts))
+        else:
+            codec.float_decompress(ft, rows, outs, ok, dsz, 10, False, temp=temp, out_capacity=list(counts))
+
+    tc = timed(ours_c, steps)
+    csz = sizes.cpu().numpy().astype(np.int64)
+    td = timed(ours_d, steps)
+    assert ok.cpu().numpy().all()
+    for i in (0, n - 1):
+        assert torch.equal(outs[i], ins[i].view(torch.uint8).reshape(-1)[: counts[i] * wb]), "round trip mismatch"
+    Ctot = int(csz.sum())
+    res.update(ratio=round(Ctot / U, 4),
+               ours={"compress_GBps": round(U / tc / 1e6, 1), "decompress_GBps": round(U / td / 1e6, 1),
+                     "compress_ms": round(tc, 4), "decompress_ms": round(td, 4),
+                     "compress_hbm_frac": round((U + Ctot) / tc / 1e6 / PEAK, 3),
+                     "decompress_hbm_frac": round((U + Ctot) / td / 1e6 / PEAK, 3)})
+    if REF is not None:
+        rt = torch.empty(max(int(3 * U), 1 << 30), dtype=torch.uint8, device="cuda")
+        rsizes = torch.zeros(n, dtype=torch.int32, device="cuda")
+        rcomp = torch.zeros_like(comp)
+        rrows = [rcomp[i] for i in range(n)]
+        tp, tb = C.c_void_p(rt.data_ptr()), C.c_size_t(rt.numel())
+
+        def ref_c():
+            if kind == "ans":
+                REF.ref_ans_encode_batch_pointer(tp, tb, 10, 0, n, pa(ins), u32(counts), None, pa(rrows),
+                                                 C.c_void_p(rsizes.data_ptr()), stream())
+            else:
+                fn = REF.ref_float_compress_sparse if sparse else REF.ref_float_compress
+                fn(tp, tb, ft, 10, 0, n, pa(ins), u32(counts), pa(rrows), C.c_void_p(rsizes.data_ptr()), stream())
+
+        def ref_d():
+            if kind == "ans":
+                REF.ref_ans_decode_batch_pointer(tp, tb, 10, 0, n, pa(rrows), pa(outs), u32(counts),
+                                                 C.c_void_p(ok.data_ptr()), C.c_void_p(dsz.data_ptr()), stream())
+            else:
+                fn = REF.ref_float_decompress_sparse if sparse else REF.ref_float_decompress
+                fn(tp, tb, ft, 10, 0, n, pa(rrows), pa(outs), u32(counts), C.c_void_p(ok.data_ptr()),
+                   C.c_void_p(dsz.data_ptr()), stream())
+
+        rtc = timed(ref_c, steps)
+        rtd = timed(ref_d, steps)
+        same = bool((rsizes.cpu().numpy().astype(np.int64) == csz).all())
+        res["reference"] = {"compress_GBps": round(U / rtc / 1e6, 1), "decompress_GBps": round(U / rtd / 1e6, 1),
+                            "compress_ms": round(rtc, 4), "decompress_ms": round(rtd, 4), "same_sizes": same}
+        res["speedup"] = {"compress": round(rtc / tc, 3), "decompress": round(rtd / td, 3),
+                          "round_trip": round((rtc + rtd) / (tc + td), 3)}
+        del rt
+    print(json.dumps(res), flush=True)
+    del temp, comp, outs
+    torch.cuda.empty_cache()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    only = set(a.only.split(",")) if a.only else None
+    torch.cuda.set_device(0)
+
+    def want(k):
+        return only is None or k in only
+
+    if want("ans"):  # config 1: 16 x 1 MiB skewed bytes, lambda = 20
+        ins = []
+        for e in range(16):
+            rng = np.random.default_rng(1000 + e)
+            b = np.minimum(255, np.floor(256 * np.minimum(rng.exponential(1 / 20.0, 1 << 20), 1.0))).astype(np.uint8)
+            ins.append(torch.from_numpy(b).cuda())
+        run_config("ANS bytes 16 x 1 MiB lambda=20", "ans", 0, ins, [1 << 20] * 16, a.steps)
+    g = torch.Generator(device="cuda")
+    if want("bf16"):  # config 2
+        g.manual_seed(2000)
+        ins = [(torch.randn(1 << 21, device="cuda", generator=g) * 0.02).to(torch.bfloat16) for _ in range(128)]
+        run_config("bf16 128 x 4 MiB N(0,0.02)", "float", codec.BFLOAT16, ins, [1 << 21] * 128, a.steps)
+    if want("f16"):
+        g.manual_seed(2001)
+        ins = [(torch.randn(1 << 21, device="cuda", generator=g) * 0.02).to(torch.float16) for _ in range(128)]
+        run_config("fp16 128 x 4 MiB N(0,0.02)", "float", codec.FLOAT16, ins, [1 << 21] * 128, a.steps)
+    if want("f32_1g"):  # config 3 (i)
+        g.manual_seed(3000)
+        ins = [torch.randn(1 << 28, device="cuda", generator=g)]
+        run_config("fp32 1 x 1 GiB N(0,1)", "float", codec.FLOAT32, ins, [1 << 28], a.steps)
+    if want("f32_64"):  # config 3 (ii)
+        g.manual_seed(3000)
+        ins = [torch.randn(1 << 22, device="cuda", generator=g) for _ in range(64)]
+        run_config("fp32 64 x 16 MiB N(0,1)", "float", codec.FLOAT32, ins, [1 << 22] * 64, a.steps)
+    if want("f64"):  # config 4
+        g.manual_seed(4000)
+        ins = [torch.randn(1 << 20, device="cuda", generator=g, dtype=torch.float64) for _ in range(16)]
+        run_config("fp64 16 x 8 MiB N(0,1)", "float", codec.FLOAT64, ins, [1 << 20] * 16, a.steps)
+    if want("sparse"):  # config 4
+        g.manual_seed(4001)
+        ins = []
+        for _ in range(16):
+            t = torch.randn(1 << 22, device="cuda", generator=g)
+            t[torch.rand(1 << 22, device="cuda", generator=g) < 0.9] = 0
+            ins.append(t)
+        run_config("sparse fp32 16 x 16 MiB, 90% zeros", "float", codec.FLOAT32, ins, [1 << 22] * 16, a.steps, sparse=True)
+
+
+if __name__ == "__main__":
+    main()
