@@ -326,7 +326,7 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
   p.tileBegin = r.tile0;
   p.tileEnd = r.tile1;
   p.totalWarps = 0;
-  p.runShift = 1;
+  p.runShift = 2;
 }
 
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {

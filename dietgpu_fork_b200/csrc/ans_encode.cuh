@@ -2,6 +2,8 @@
 // fused split + normalise + encode kernel (fused.cu): table normalisation, the rANS row step and the
 // warp-level "encode one run of blocks" routine.
 #pragma once
+#include <cstdlib>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -154,7 +156,7 @@ struct EncParams {
   uint32_t* runCounter; // zeroed; hands out runs beyond each warp's first one
   uint32_t totalWarps;
   uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
-  uint32_t runShift;           // log2(runs per tile): runs are 8 >> runShift consecutive blocks (4 for large batches)
+  uint32_t runShift;           // log2(runs per tile): runs are 8 >> runShift consecutive blocks
   // fused kernel only: per-element flag, non-zero once the element's exponent plane and table are complete
   const uint32_t* ready;
 };
@@ -166,10 +168,12 @@ constexpr uint32_t kEncCtasPerSm = 10;
 constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
 constexpr uint32_t kEncChunkRows = 16;            // rows per staged symbol chunk (512 symbols, one 16-byte load per lane)
 constexpr uint32_t kEncChunk = kEncChunkRows * 32;
-// Run = consecutive blocks one warp encodes as one stream: 4 (half a tile) when there is enough work to fill the
-// GPU with such runs, 2 or 1 for small batches.
+// Run = consecutive blocks one warp encodes as one stream: 2 when there is enough work to fill the GPU with such
+// runs, 1 for small batches. (4-block runs amortise the per-run start-up slightly better but leave a long
+// tail: a run then takes ~100 us of wall time with 40 warps per SM; fused kernel 0.42 ms vs 0.386 ms.)
 inline uint32_t chooseRunShift(uint32_t totalTiles, uint32_t warpsWanted) {
-  uint32_t shift = 1;
+  uint32_t shift = 2;
+  if (const char* e = getenv("DGB_RUN_SHIFT")) return (uint32_t)atoi(e); // experiment knob
   while (shift < 3 && (totalTiles << shift) < warpsWanted) ++shift;
   return shift;
 }

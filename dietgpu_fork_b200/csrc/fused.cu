@@ -15,7 +15,9 @@
 //     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
 //   * a split CTA that finds no tile left becomes an encode CTA.
 // Split CTAs never wait, so the flags always arrive; the grid is sized to be co-resident.
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include "ans_encode.cuh"
 #include "float_split.cuh"
@@ -33,6 +35,7 @@ struct FusedParams {
   uint32_t* ready;        // [numElems] zeroed
   uint32_t totalTiles;
   uint32_t splitCtasPerSm;
+  unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run start, end, smid/role}
 };
 
 constexpr uint32_t kFusedThreads = kEncWarps * 32; // 128
@@ -48,11 +51,15 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint32_t sBcast[2];
   const uint32_t tid = threadIdx.x;
+  unsigned long long t0 = 0, t1 = 0, t2 = 0;
+  uint32_t smidTrace = 0;
+  if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
 
   if (tid == 0) {
     uint32_t smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
     sBcast[0] = atomicAdd(&p.smTicket[smid & 511u], 1u) < p.splitCtasPerSm ? 1u : 0u;
+    smidTrace = smid;
   }
   __syncthreads();
   const bool splitRole = sBcast[0] != 0;
@@ -102,6 +109,7 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     __syncthreads();
   }
 
+  if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
   // ---- encode role ----
   EncWarp w;
   w.init(smem + (tid >> 5) * kEncWarpSmem);
@@ -113,7 +121,14 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     uint32_t nextRun = 0;
     if (w.lane == 0) nextRun = atomicAdd(p.ep.runCounter, 1u);
     encodeRun<PB, true>(p.ep, w, run);
+    if (p.trace && tid == 0 && t2 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); // end of first run
     run = __shfl_sync(0xffffffffu, nextRun, 0);
+  }
+  if (p.trace && tid == 0) {
+    unsigned long long t3;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t3));
+    unsigned long long* r = p.trace + 5ull * blockIdx.x;
+    r[0] = t0; r[1] = t1; r[2] = t2; r[3] = t3; r[4] = ((unsigned long long)smidTrace << 1) | (splitRole ? 1u : 0u);
   }
 }
 
@@ -135,11 +150,25 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   p.ep.runShift = chooseRunShift(p.totalTiles, (uint32_t)smCount() * kEncCtasPerSm * kEncWarps);
   const uint32_t want = divUp(p.totalTiles << p.ep.runShift, kEncWarps) + p.totalTiles;
   const uint32_t grid = min(want, (uint32_t)smCount() * (uint32_t)perSm);
+  static const char* tracePath = getenv("DGB_FUSED_TRACE"); // debugging aid: per-CTA timeline of the last launch
+  p.trace = nullptr;
+  if (tracePath) DGB_CUDA(cudaMalloc(&p.trace, 5ull * 8 * grid));
   {
     ProfScope ps__("k_compressFused", s);
     kern<<<grid, kFusedThreads, kFusedSmem, s>>>(p);
   }
   DGB_CUDA(cudaGetLastError());
+  if (tracePath) {
+    std::vector<unsigned long long> h(5ull * grid);
+    DGB_CUDA(cudaMemcpyAsync(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost, s));
+    DGB_CUDA(cudaStreamSynchronize(s));
+    cudaFree(p.trace);
+    if (FILE* f = fopen(tracePath, "w")) {
+      for (uint32_t i = 0; i < grid; ++i)
+        fprintf(f, "%u %llu %llu %llu %llu %llu\n", i, h[5 * i], h[5 * i + 1], h[5 * i + 2], h[5 * i + 3], h[5 * i + 4]);
+      fclose(f);
+    }
+  }
   return kOk;
 }
 
