@@ -11,6 +11,8 @@
 // then writes the tile out with 16-byte vectors: plain bytes, or float words joined with the raw
 // section. fp64 decodes both exponent planes of the tile before the join, so it is single pass
 // too (the reference always takes two passes for fp64, GpuFloatDecompress.cuh:932-935).
+#include <cstdlib>
+
 #include "float_math.cuh"
 #include "internal.h"
 #include "prof.h"
@@ -21,7 +23,8 @@ struct DecParams {
   DecodeArgs a;
   const DecInfo* info;  // [planes][numElems]
   const uint32_t* lut;  // [planes][numElems][1 << probBits]
-  uint32_t tilesPerCta; // every CTA owns a contiguous range of 8-block tiles
+  uint32_t claimTiles;  // consecutive 8-block tiles a CTA takes per claim
+  uint32_t* tileCounter; // zeroed by k_decodePrep; claims beyond each CTA's first one
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -30,10 +33,11 @@ struct DecParams {
 //   entry = (slot - cdf[sym]) << 20 | pdf[sym] << 8 | sym.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_decodePrep(const DecodeArgs a, DecInfo* __restrict__ info,
-                                                    uint32_t* __restrict__ lut) {
+                                                    uint32_t* __restrict__ lut, uint32_t* __restrict__ tileCounter) {
   __shared__ uint32_t sCdf[257];
   __shared__ uint32_t sWarp[8];
   const uint32_t e = blockIdx.x, plane = blockIdx.y, s = threadIdx.x, lane = s & 31, w = s >> 5;
+  if (e == 0 && plane == 0 && s == 0) *tileCounter = 0; // k_decode's dynamic tile claims start here
   const Elem el = a.elems[e];
   const uint8_t* arch = (const uint8_t*)el.in;
   uint32_t n, reportN;
@@ -146,24 +150,25 @@ template <int PB, int FT> __host__ __device__ constexpr uint32_t decCtaSmem() {
 struct DecCtx {
   uint32_t state;
   uint32_t ptrBytes;   // 2 * (index one past the next word to read)
-  int reqLo, readyLo;  // lowest piece requested / waited for
+  int cur;             // 1 KB piece holding the next word to read (-1: the block has no words)
+  uint32_t pend;       // bit s: ring slot s has a copy in flight that has not been waited for
   const uint8_t* src;  // this block's first payload word
   uint32_t totalBytes; // roundUp(words, 8) * 2
   uint32_t ringAddr, bar0, lutAddr;
 };
 
-__device__ __forceinline__ void decRequest(DecCtx& c, int upTo, uint32_t lane) {
-  // request pieces reqLo-1 ... upTo (descending); slot = piece & 1
-  while (c.reqLo > upTo) {
-    --c.reqLo;
-    if (lane == 0) {
-      const uint32_t off = (uint32_t)c.reqLo * kPieceWords * 2;
-      const uint32_t bytes = min(kPieceWords * 2, c.totalBytes - off);
-      const uint32_t slot = (uint32_t)c.reqLo & 1u;
-      mbarExpectTx(c.bar0 + 8 * slot, bytes);
-      bulkLoad(c.ringAddr + slot * kPieceWords * 2, c.src + off, bytes, c.bar0 + 8 * slot);
-    }
+// Ring protocol: pieces `cur` and `cur - 1` are resident or in flight (slot = piece & 1). A 16-row chunk reads
+// at most 1 KB, so it crosses at most one piece boundary; when it has, the slot of the piece left behind takes
+// piece `cur - 1` (new cur), which is waited for at the start of the next chunk.
+__device__ __forceinline__ void decRequest(DecCtx& c, int piece, uint32_t lane) {
+  const uint32_t slot = (uint32_t)piece & 1u;
+  if (lane == 0) {
+    const uint32_t off = (uint32_t)piece * kPieceWords * 2;
+    const uint32_t bytes = min(kPieceWords * 2, c.totalBytes - off);
+    mbarExpectTx(c.bar0 + 8 * slot, bytes);
+    bulkLoad(c.ringAddr + slot * kPieceWords * 2, c.src + off, bytes, c.bar0 + 8 * slot);
   }
+  c.pend |= 1u << slot;
 }
 
 // One decode step of a full symbol row (dietgpu/ans/GpuANSDecode.cuh:55-90, :174-217): LUT lookup, state
@@ -294,6 +299,42 @@ __device__ __forceinline__ void writeChunk(const RawSections& rs, uint8_t* outBa
   }
 }
 
+// Full 512-word chunk, 16-byte aligned output, raw bytes staged in shared memory: fixed trip counts and
+// shared-memory addresses only (the general writeChunk handles everything else).
+template <int FT>
+__device__ __forceinline__ void writeChunkFull(uint32_t symAddr, uint32_t rawAddr, uint4* out, uint32_t lane) {
+  if constexpr (FT == kFtF16 || FT == kFtBF16) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const uint32_t i = lane + 32 * k;
+      uint2 e, r;
+      asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(symAddr + i * 8));
+      asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(rawAddr + i * 8));
+      uint32_t y0 = __byte_perm(r.x, e.x, 0x5140), y1 = __byte_perm(r.x, e.x, 0x7362);
+      uint32_t y2 = __byte_perm(r.y, e.y, 0x5140), y3 = __byte_perm(r.y, e.y, 0x7362);
+      if constexpr (FT == kFtBF16) {
+        y0 = rotr1x2(y0); y1 = rotr1x2(y1); y2 = rotr1x2(y2); y3 = rotr1x2(y3);
+      }
+      out[i] = make_uint4(y0, y1, y2, y3);
+    }
+  } else { // kFtF32: 128 groups of 4 words; lo = 2 bytes per word at rawAddr, hi = 1 byte per word after 1 KB
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t i = lane + 32 * k;
+      uint32_t e, hi;
+      uint2 lo;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(symAddr + i * 4));
+      asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo.x), "=r"(lo.y) : "r"(rawAddr + i * 8));
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"(rawAddr + 2 * kDecChunk + i * 4));
+      const uint32_t t01 = __byte_perm(hi, e, 0x5140), t23 = __byte_perm(hi, e, 0x7362);
+      const uint32_t v0 = __byte_perm(lo.x, t01, 0x5410), v1 = __byte_perm(lo.x, t01, 0x7632);
+      const uint32_t v2 = __byte_perm(lo.y, t23, 0x5410), v3 = __byte_perm(lo.y, t23, 0x7632);
+      out[i] = make_uint4(__funnelshift_r(v0, v0, 1), __funnelshift_r(v1, v1, 1), __funnelshift_r(v2, v2, 1),
+                          __funnelshift_r(v3, v3, 1));
+    }
+  }
+}
+
 template <int PB, int FT>
 __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode(const DecParams p) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
@@ -328,9 +369,15 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
   const uint32_t geMask = laneMaskGe();
   const DecodeArgs& a = p.a;
 
-  const uint32_t t0 = blockIdx.x * p.tilesPerCta;
-  const uint32_t t1 = min(t0 + p.tilesPerCta, a.totalTiles);
+  // Tiles are claimed in order, `claimTiles` at a time (first claim static), so the CTAs finish together.
+  __shared__ uint32_t sNext;
   uint32_t cur = 0xffffffffu;
+  uint32_t claim = blockIdx.x;
+  for (;;) {
+    const uint32_t t0 = claim * p.claimTiles;
+    if (t0 >= a.totalTiles) break;
+    const uint32_t t1 = min(t0 + p.claimTiles, a.totalTiles);
+    if (tid == 0) sNext = gridDim.x + atomicAdd(p.tileCounter, 1u);
   for (uint32_t tile = t0; tile < t1; ++tile) {
     const uint32_t e = findElement(&a.elems[0].tileBase, sizeof(Elem) / 4, a.numElems, tile, cur);
     if (e != cur) { // CTA-uniform: every warp of the CTA walks the same tile sequence
@@ -363,10 +410,11 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
       c.src = ans + ansOverhead(nb) + 2 * (size_t)bw.y;
       c.totalBytes = roundUp(words, 8) * 2;
       c.ptrBytes = words * 2;
-      const int top = words ? (int)((words - 1) / kPieceWords) : -1;
-      c.reqLo = c.readyLo = top + 1;
+      c.cur = words ? (int)((words - 1) / kPieceWords) : -1;
+      c.pend = 0;
       __syncwarp(); // every lane is done with the ring of the previous block
-      decRequest(c, max(top - 1, 0), lane);
+      if (c.cur >= 0) decRequest(c, c.cur, lane);
+      if (c.cur >= 1) decRequest(c, c.cur - 1, lane);
     }
     uint8_t* outBase;
     if constexpr (FT == kFtNone) outBase = (uint8_t*)el.out + (size_t)blk * kBlockSyms;
@@ -377,6 +425,7 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
     RawSections rsGlobal;
     rsGlobal.a = rsGlobal.b = nullptr;
     bool rawAligned = false;
+    const bool outAligned = (((uintptr_t)outBase) & 15u) == 0;
     if constexpr (FT != kFtNone) {
       rsGlobal = rawSections(FT, (uint8_t*)d0.fbase + kFloatHeaderBytes, d0.n);
       rawAligned = (((uintptr_t)d0.fbase) & 15u) == 0;
@@ -395,14 +444,15 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
 #pragma unroll
       for (int pl = 0; pl < kPlanes; ++pl) {
         DecCtx& cx = ctx[pl];
-        // the piece under the read pointer and the one below must have landed
-        const int q = cx.ptrBytes ? (int)((cx.ptrBytes / 2 - 1) / kPieceWords) : -1;
-        const int need = q >= 0 ? max(q - 1, 0) : 0x7fffffff;
-        while (cx.readyLo > need) {
-          --cx.readyLo;
-          const uint32_t slot = (uint32_t)cx.readyLo & 1u;
-          mbarWait(cx.bar0 + 8 * slot, (phaseBits >> (2 * pl + slot)) & 1u);
-          phaseBits ^= 1u << (2 * pl + slot);
+        if (cx.pend) { // copies requested since the last chunk must have landed
+#pragma unroll
+          for (uint32_t slot = 0; slot < 2; ++slot) {
+            if (cx.pend & (1u << slot)) {
+              mbarWait(cx.bar0 + 8 * slot, (phaseBits >> (2 * pl + slot)) & 1u);
+              phaseBits ^= 1u << (2 * pl + slot);
+            }
+          }
+          cx.pend = 0;
         }
         uint32_t state = cx.state, ptrBytes = cx.ptrBytes;
         const uint32_t symAddr = smemAddr(trans[pl]) + lane;
@@ -425,18 +475,32 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode
         }
         cx.state = state;
         cx.ptrBytes = ptrBytes;
-        // keep the piece under the new read pointer and the one below it in flight
-        const int nq = ptrBytes ? (int)((ptrBytes / 2 - 1) / kPieceWords) : -1;
-        if (nq >= 1 && cx.reqLo > nq - 1) {
-          __syncwarp(); // all lanes are past their reads of the slot being refilled
-          decRequest(cx, nq - 1, lane);
+        // crossed into the piece below: the slot left behind takes the next lower piece
+        if (cx.cur >= 1 && ptrBytes <= (uint32_t)cx.cur * (kPieceWords * 2)) {
+          cx.cur -= 1;
+          if (cx.cur >= 1) {
+            __syncwarp(); // all lanes are past their reads of the slot being refilled
+            decRequest(cx, cx.cur - 1, lane);
+          }
         }
       }
       if constexpr (decRawStage<FT>() != 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncwarp();
-      writeChunk<FT>(rs, outBase, wordOff, len, trans[0], trans[kPlanes - 1], lane);
+      bool done = false;
+      if constexpr (decRawStage<FT>() != 0) {
+        if (len == kDecChunk && rawAligned && outAligned) {
+          writeChunkFull<FT>(smemAddr(trans[0]), smemAddr(rawStage),
+                             (uint4*)outBase + wordOff / FloatTraits<FT == kFtNone ? kFtF16 : FT>::kGroup, lane);
+          done = true;
+        }
+      }
+      if (!done) writeChunk<FT>(rs, outBase, wordOff, len, trans[0], trans[kPlanes - 1], lane);
       __syncwarp(); // transposer and raw stage are reused by the next chunk
     }
+  }
+    __syncthreads();
+    claim = sNext;
+    __syncthreads();
   }
 }
 
@@ -447,8 +511,10 @@ static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   const uint32_t perSm = FT == kFtF64 ? 3u : 6u;
   uint32_t ctas = min(p.a.totalTiles, (uint32_t)smCount() * perSm);
-  p.tilesPerCta = divUp(p.a.totalTiles, ctas);
-  ctas = divUp(p.a.totalTiles, p.tilesPerCta);
+  p.claimTiles = 1; // measured on B200 (bf16, 128 x 4 MiB): 1: 0.300, 2: 0.307, 3: 0.320, 4: 0.327 ms; static ranges: 0.359 ms
+  if (const char* e = getenv("DGB_DEC_CLAIM")) p.claimTiles = (uint32_t)max(1, atoi(e)); // experiment knob
+  if (p.a.totalTiles < ctas * p.claimTiles) p.claimTiles = 1;
+  ctas = min(ctas, divUp(p.a.totalTiles, p.claimTiles));
   {
     ProfScope ps__("k_decode", s);
     k_decode<PB, FT><<<ctas, kDecWarps * 32, smemBytes, s>>>(p);
@@ -475,17 +541,19 @@ int launchDecode(Temp& tmp, const DecodeArgs& a, cudaStream_t s) {
   const int planes = a.floatType == kFtF64 ? 2 : 1;
   DecInfo* info = tmp.alloc<DecInfo>((size_t)planes * a.numElems);
   uint32_t* lut = tmp.alloc<uint32_t>(((size_t)planes * a.numElems) << a.probBits);
+  uint32_t* counter = tmp.alloc<uint32_t>(4);
   if (tmp.failed()) return kErrCuda;
   {
     ProfScope ps__("k_decodePrep", s);
-    k_decodePrep<<<dim3(a.numElems, planes), 256, 0, s>>>(a, info, lut);
+    k_decodePrep<<<dim3(a.numElems, planes), 256, 0, s>>>(a, info, lut, counter);
   }
   DGB_CUDA(cudaGetLastError());
   DecParams p;
   p.a = a;
   p.info = info;
   p.lut = lut;
-  p.tilesPerCta = 1;
+  p.claimTiles = 1;
+  p.tileCounter = counter;
   if (a.totalTiles == 0) return kOk;
   switch (a.probBits) {
     case 9: return launchDecodeFt<9>(p, s);
