@@ -280,6 +280,9 @@ __device__ __forceinline__ uint32_t ldRelaxed(const uint32_t* p) {
   asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void redRelease(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -464,6 +467,107 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     }
   }
   if (runSyms & (kBlockSyms - 1)) flush(true); // the partial block
+}
+
+// ---------------------------------------------------------------------------------------------
+// Compaction of one 8-block tile by ONE warp (the fused kernel's in-launch version of k_coalesce,
+// ans_encode.cu): exclusive prefix of the tile from the per-group sums and the block sizes before it,
+// payload copy scratch slot -> archive, block index entries; tile 0 also writes the pdf table, the last
+// tile the header, firstCompSegmentBytes and outSize (dietgpu/ans/GpuANSEncode.cuh:533-623). Every size
+// of the element must be final and visible (the caller acquired the element's completion count);
+// everything another SM produced is read through L2 (.cg). Deliberately not inlined: it runs once per 8 blocks
+// and must not take registers from the row loop (the caller passes its __grid_constant__ parameter block).
+// ---------------------------------------------------------------------------------------------
+static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int probBits, uint32_t e, uint32_t tk, uint32_t lane) {
+  const EncodeArgs& a = p.a;
+  const Elem el = a.elems[e];
+  const uint32_t t = tk - el.tileBase;
+  const uint32_t n = a.nDev ? a.nDev[e] : el.n;
+  const uint32_t nb = divUp(n, kBlockSyms);
+  const uint32_t numTiles = max(1u, divUp(nb, kTileBlocks));
+  if (t >= numTiles) return;
+  uint8_t* ans = (uint8_t*)el.out;
+  uint8_t* fbase = nullptr;
+  if (a.floatType != kFtNone) {
+    fbase = (uint8_t*)el.out + el.sizeBias;
+    ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
+    if (a.round) ans += *(const uint32_t*)(fbase + 16);
+  }
+  const uint32_t firstBlk = t * kTileBlocks;
+  const uint32_t grp = firstBlk / kGroupBlocks;
+  const uint32_t* groupSum = p.groupWords + el.groupBase;
+  const uint32_t* bwords = p.blockWords + el.blockBase;
+  uint32_t part = 0;
+  for (uint32_t g = lane; g < grp; g += 32) part += __ldcg(groupSum + g);
+  for (uint32_t b = grp * kGroupBlocks + lane; b < firstBlk; b += 32) part += roundUp(__ldcg(bwords + b), 8);
+  const uint32_t excl = warpSum(part);
+  // lane j < 8 owns block firstBlk + j
+  const uint32_t myBlk = firstBlk + lane;
+  uint32_t words = 0, blkLen = 0;
+  if (lane < kTileBlocks && myBlk < nb) {
+    words = __ldcg(bwords + myBlk);
+    blkLen = min(kBlockSyms, n - myBlk * kBlockSyms);
+  }
+  const uint32_t padded = roundUp(words, 8);
+  uint32_t incl = padded;
+#pragma unroll
+  for (int o = 1; o < (int)kTileBlocks; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= (uint32_t)o) incl += v;
+  }
+  const uint32_t startWord = excl + incl - padded;
+  const uint32_t tileWords = __shfl_sync(0xffffffffu, incl, kTileBlocks - 1);
+  if (blkLen) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[myBlk] = make_uint2((blkLen << 16) | words, startWord);
+  uint8_t* payload = ans + ansOverhead(nb);
+  const uint8_t* slots = p.scratch + (size_t)(el.blockBase + firstBlk) * kSlotBytes;
+  // two blocks at a time, up to two 16-byte vectors per lane and block in flight
+#pragma unroll 1
+  for (uint32_t j = 0; j < kTileBlocks; j += 2) {
+    const uint32_t nvA = __shfl_sync(0xffffffffu, padded, j) >> 3, nvB = __shfl_sync(0xffffffffu, padded, j + 1) >> 3;
+    const uint32_t stA = __shfl_sync(0xffffffffu, startWord, j), stB = __shfl_sync(0xffffffffu, startWord, j + 1);
+    if ((nvA | nvB) == 0) continue;
+    const uint4* srcA = (const uint4*)(slots + (size_t)j * kSlotBytes);
+    const uint4* srcB = (const uint4*)(slots + (size_t)(j + 1) * kSlotBytes);
+    uint4* dstA = (uint4*)(payload + 2 * (size_t)stA);
+    uint4* dstB = (uint4*)(payload + 2 * (size_t)stB);
+    uint4 a0, a1, b0, b1;
+    a0 = a1 = b0 = b1 = make_uint4(0, 0, 0, 0);
+    if (lane < nvA) a0 = __ldcg(srcA + lane);
+    if (lane + 32 < nvA) a1 = __ldcg(srcA + lane + 32);
+    if (lane < nvB) b0 = __ldcg(srcB + lane);
+    if (lane + 32 < nvB) b1 = __ldcg(srcB + lane + 32);
+    if (lane < nvA) dstA[lane] = a0;
+    if (lane + 32 < nvA) dstA[lane + 32] = a1;
+    if (lane < nvB) dstB[lane] = b0;
+    if (lane + 32 < nvB) dstB[lane + 32] = b1;
+    for (uint32_t i = lane + 64; i < nvA; i += 32) dstA[i] = __ldcg(srcA + i);
+    for (uint32_t i = lane + 64; i < nvB; i += 32) dstB[i] = __ldcg(srcB + i);
+  }
+  if (t == 0) { // pdf table; zero for absent symbols and for an empty element
+    const uint2* tab = p.table + (size_t)e * 256;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint2 en = __ldcg(tab + lane + 32 * k);
+      const uint32_t pdf = (n && en.x) ? (1u << probBits) - (en.y & 0xfffu) : 0u;
+      ((uint16_t*)(ans + kAnsHeaderBytes))[lane + 32 * k] = (uint16_t)pdf;
+    }
+  }
+  if (t == numTiles - 1 && lane == 0) {
+    const uint32_t totalWords = excl + tileWords;
+    const uint32_t cs = (a.useChecksum && a.checksum) ? __ldcg(a.checksum + e) : 0u;
+    uint4* h = (uint4*)ans;
+    h[0] = make_uint4(kAnsMagic, nb, n, totalWords);
+    h[1] = make_uint4((uint32_t)probBits | (a.useChecksum ? 16u : 0u), cs, 0u, 0u);
+    if (nb & 1u) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[nb] = make_uint2(0u, 0u);
+    const uint32_t total = ansOverhead(nb) + 2u * totalWords;
+    if (a.floatType != kFtNone && a.round == 0) *(uint32_t*)(fbase + 16) = total;
+    if (a.outSize) {
+      if (a.round) a.outSize[e] += total;
+      else
+        a.outSize[e] = el.sizeBias + total +
+                       (a.floatType != kFtNone ? kFloatHeaderBytes + floatRawBytes(a.floatType, n) : 0u);
+    }
+  }
 }
 
 } // namespace dgb

@@ -1,5 +1,5 @@
-// Fused float compress for sm_100a: float split, table normalisation and rANS block encoding of the exponent
-// plane in ONE persistent launch (then k_coalesce).
+// Fused float compress for sm_100a: float split, table normalisation, rANS block encoding of the exponent
+// plane and compaction of the encoded blocks into the archive in ONE persistent launch.
 //
 // Why: measured on B200 the split is bound by shared-memory atomic throughput and the
 // encoder by instruction issue; run back to back they add up, run on the same SMs at the same time they
@@ -13,8 +13,13 @@
 //     table and publishes the element's ready flag (release);
 //   * encode warps claim runs of 4 blocks in the same order, wait (acquire) for the run's element, and encode
 //     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
-//   * a split CTA that finds no tile left becomes an encode CTA.
-// Split CTAs never wait, so the flags always arrive; the grid is sized to be co-resident.
+//   * a split CTA that finds no tile left becomes an encode CTA;
+//   * compaction (what k_coalesce does for the stand-alone encoder) is the warps' last job: every finished run
+//     bumps its element's run count (release); a warp that finds no run left takes tickets for 8-block compaction
+//     tiles, waits until the tile's element is completely encoded and copies the tile's blocks from their
+//     L2-resident scratch slots to their final place (every run is by then owned by a running warp).
+// Split CTAs never wait and encode warps wait only for split CTAs, so every flag arrives; the grid is sized to be
+// co-resident.
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -33,6 +38,8 @@ struct FusedParams {
   uint32_t* smTicket;     // [512] zeroed
   uint32_t* tilesDone;    // [numElems] zeroed
   uint32_t* ready;        // [numElems] zeroed
+  uint32_t* runsDone;     // [numElems] zeroed: finished encode runs per element
+  uint32_t* coalClaim;    // zeroed: next compaction tile to hand out (nullptr: k_coalesce runs as a second launch)
   uint32_t totalTiles;
   uint32_t splitCtasPerSm;
   unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run start, end, smid/role}
@@ -46,7 +53,7 @@ constexpr uint32_t kFusedSmem =
     kEncWarps * kEncWarpSmem > kFusedHistBytes + kFusedNormBytes ? kEncWarps * kEncWarpSmem : kFusedHistBytes + kFusedNormBytes;
 
 template <int FT, int PB>
-__global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(const FusedParams p) {
+__global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(const __grid_constant__ FusedParams p) {
   static_assert(FloatTraits<FT>::kPlanes == 1, "single exponent plane only");
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint32_t sBcast[2];
@@ -122,7 +129,32 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     if (w.lane == 0) nextRun = atomicAdd(p.ep.runCounter, 1u);
     encodeRun<PB, true>(p.ep, w, run);
     if (p.trace && tid == 0 && t2 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); // end of first run
+    if (p.coalClaim) { // this run's slots, sizes and states, then its count (release)
+      __syncwarp();
+      if (w.lane == 0) redRelease(p.runsDone + w.curElem, 1u);
+    }
     run = __shfl_sync(0xffffffffu, nextRun, 0);
+  }
+  // Compaction: warps that ran out of runs take tickets for 8-block tiles in order and wait until the tile's
+  // element is completely encoded. Every run is by now owned by a running warp that waits for nothing but split
+  // CTAs, so the wait cannot deadlock; elements finish in order, so early finishers find work immediately.
+  if (p.coalClaim) {
+    uint32_t guess = 0;
+    for (;;) {
+      uint32_t tk = 0;
+      if (w.lane == 0) tk = atomicAdd(p.coalClaim, 1u);
+      tk = __shfl_sync(0xffffffffu, tk, 0);
+      if (tk >= p.totalTiles) break;
+      const uint32_t ce = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tk, guess);
+      guess = ce;
+      if (w.lane == 0) {
+        const uint32_t want = (p.sp.elems[ce + 1].tileBase - p.sp.elems[ce].tileBase) << p.ep.runShift;
+        while (ldRelaxed(p.runsDone + ce) != want) __nanosleep(200);
+        (void)ldAcquire(p.runsDone + ce);
+      }
+      __syncwarp();
+      coalesceTileWarp(p.ep, PB, ce, tk, w.lane);
+    }
   }
   if (p.trace && tid == 0) {
     unsigned long long t3;
@@ -206,6 +238,9 @@ int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& e
   p.smTicket = es.fusedCtrl + 1;
   p.tilesDone = es.fusedCtrl + kFusedCtrlFixed;
   p.ready = p.tilesDone + a.numElems;
+  p.runsDone = p.ready + a.numElems;
+  static const bool separateCoalesce = getenv("DGB_FUSED_COALESCE") && atoi(getenv("DGB_FUSED_COALESCE")) == 0;
+  p.coalClaim = separateCoalesce ? nullptr : es.fusedCtrl + kFusedCtrlFixed - 1; // experiment knob
   p.ep.ready = p.ready;
   p.totalTiles = totalTiles;
   int rc;
@@ -216,7 +251,7 @@ int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& e
     default: return kErrInvalidArg;
   }
   if (rc) return rc;
-  return launchCoalesce(a, es, all, s);
+  return p.coalClaim ? kOk : launchCoalesce(a, es, all, s);
 }
 
 } // namespace dgb

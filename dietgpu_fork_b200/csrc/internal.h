@@ -131,7 +131,7 @@ struct EncodeArgs {
 };
 // Enqueues normalise + encode for one exponent plane / byte stream. Scratch comes from `tmp`.
 // A slice of the work list: elements [e0, e1) with their 8-block tiles and 4096-symbol blocks.
-constexpr uint32_t kFusedCtrlFixed = 1 + 512; // split tile counter + per-SM role tickets
+constexpr uint32_t kFusedCtrlFixed = 1 + 512 + 1; // split tile counter + per-SM role tickets + compaction claim counter
 
 struct WorkRange {
   uint32_t e0, e1, tile0, tile1, blk0, blk1;
@@ -142,7 +142,7 @@ struct EncodeScratch {
   uint32_t* blockWords;
   uint32_t* groupWords;
   uint32_t* runCounters;
-  uint32_t* fusedCtrl; // [kFusedCtrlFixed + 2 * numElems]: split counter, SM tickets | tilesDone | ready
+  uint32_t* fusedCtrl; // [kFusedCtrlFixed + 3 * numElems]: split counter, SM tickets, compaction claims | tilesDone | ready | runsDone
   uint8_t* scratch;
 };
 // totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
@@ -151,8 +151,8 @@ int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, Enc
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
 // compaction only (k_coalesce), for callers that produced the block slots themselves
 int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
-// float split + table normalisation + block encoding of one exponent plane in ONE persistent launch, then
-// k_coalesce. Single-plane float types, host-known sizes, dense input (fused.cu).
+// float split + table normalisation + block encoding + compaction of one exponent plane in ONE persistent
+// launch. Single-plane float types, host-known sizes, dense input (fused.cu).
 int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
                              const uint32_t* checksum, int useChecksum, cudaStream_t s);
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
