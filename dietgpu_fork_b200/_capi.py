@@ -56,6 +56,8 @@ def _load():
     L.dgb_float_get_compressed_info.argtypes = [vp, i, u32, vp, vp, vp, vp, sz, vp]
     L.dgb_profile_launches.restype = C.c_ulonglong
     L.dgb_profile_enable.argtypes = [i]
+    L.dgb_set_fused_min_tiles.argtypes = [C.c_longlong]
+    L.dgb_set_fused_min_tiles.restype = None
     L.dgb_profile_report.argtypes = [C.c_char_p, sz]
     L.dgb_profile_report.restype = i
     for name in ("dgb_ans_encode_batch_pointer", "dgb_ans_encode_batch_stride",
@@ -73,7 +75,7 @@ lib = _load()
 # every symbol include/dietgpu_b200.h declares (checked by tests/test_capi_symbols.py)
 EXPORTS = [
     "dgb_version", "dgb_last_temp_bytes_used", "dgb_profile_launches", "dgb_profile_enable",
-    "dgb_profile_report", "dgb_ans_max_compressed_size",
+    "dgb_profile_report", "dgb_set_fused_min_tiles", "dgb_ans_max_compressed_size",
     "dgb_float_max_compressed_size", "dgb_sparse_float_max_compressed_size",
     "dgb_temp_bytes_required", "dgb_ans_encode_batch_pointer", "dgb_ans_encode_batch_stride",
     "dgb_ans_encode_batch_split_size", "dgb_ans_decode_batch_pointer", "dgb_ans_decode_batch_stride",

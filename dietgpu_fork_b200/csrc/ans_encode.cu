@@ -305,7 +305,8 @@ int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, Enc
   es.table = tmp.alloc<uint2>((size_t)a.numElems * 256);
   es.blockWords = tmp.alloc<uint32_t>(a.totalTiles);
   // one zeroed control array: group sums | run counters (one per possible launch) | fused-kernel control
-  const size_t ctrlWords = (size_t)totalGroups + a.numElems + 1 + kFusedCtrlFixed + 3 * (size_t)a.numElems;
+  const size_t ctrlWords = (size_t)totalGroups + a.numElems + 1 + kFusedCtrlFixed + 3 * (size_t)a.numElems +
+                           divUp(a.totalTiles, kTileBlocks) + a.numElems; // + fused kernel's per-tile sums (tiles <= blocks / 8 + elements)
   es.groupWords = tmp.alloc<uint32_t>(ctrlWords);
   es.scratch = (uint8_t*)tmp.alloc((size_t)a.totalTiles * kSlotBytes);
   if (tmp.failed()) return kErrCuda;
@@ -323,6 +324,7 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
   p.groupWords = es.groupWords;
   p.runCounter = es.runCounters + r.e0;
   p.ready = nullptr;
+  p.tileWords = nullptr;
   p.tileBegin = r.tile0;
   p.tileEnd = r.tile1;
   p.totalWarps = 0;

@@ -153,6 +153,7 @@ struct EncParams {
   uint8_t* scratch;     // [totalBlocks][kSlotBytes]
   uint32_t* blockWords; // [totalBlocks] words emitted per block
   uint32_t* groupWords; // [totalGroups] sum of roundUp(words, 8) per group of 256 blocks, zeroed
+  uint32_t* tileWords;  // fused kernel: [totalTiles] the same sums per 8-block tile, zeroed (nullptr otherwise)
   uint32_t* runCounter; // zeroed; hands out runs beyond each warp's first one
   uint32_t totalWarps;
   uint32_t tileBegin, tileEnd; // range of 8-block tiles handled by this launch
@@ -392,6 +393,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
       if (lane == 0) {
         p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
         atomicAdd(&w.groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
+        if (FUSED) atomicAdd(p.tileWords + w.tileBase + blk / kTileBlocks, flushedVecs * 8 + (padded >> 1));
       }
       bytes = padded;
     }
@@ -471,14 +473,18 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
 
 // ---------------------------------------------------------------------------------------------
 // Compaction of one 8-block tile by ONE warp (the fused kernel's in-launch version of k_coalesce,
-// ans_encode.cu): exclusive prefix of the tile from the per-group sums and the block sizes before it,
-// payload copy scratch slot -> archive, block index entries; tile 0 also writes the pdf table, the last
-// tile the header, firstCompSegmentBytes and outSize (dietgpu/ans/GpuANSEncode.cuh:533-623). Every size
-// of the element must be final and visible (the caller acquired the element's completion count);
-// everything another SM produced is read through L2 (.cg). Deliberately not inlined: it runs once per 8 blocks
-// and must not take registers from the row loop (the caller passes its __grid_constant__ parameter block).
+// ans_encode.cu): exclusive prefix of the tile from the per-group and per-tile sums before it, payload copy
+// scratch slot -> archive, block index entries; tile 0 also writes the pdf table, the last tile the header,
+// firstCompSegmentBytes and outSize (dietgpu/ans/GpuANSEncode.cuh:533-623). Every size of the element must be
+// final and visible (the caller acquired the element's completion count); everything another SM produced is
+// read through L2 (.cg). The payload goes through the warp's own shared memory (`stage`, kEncWarpSmem bytes,
+// free once the warp has no run left): all 16-byte cp.async loads of as many blocks as fit are in flight at
+// once, and since consecutive blocks are contiguous in the archive they leave as one contiguous copy.
+// Deliberately not inlined: it runs once per 8 blocks and must not take registers from the row loop (the caller
+// passes its __grid_constant__ parameter block).
 // ---------------------------------------------------------------------------------------------
-static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int probBits, uint32_t e, uint32_t tk, uint32_t lane) {
+static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int probBits, uint32_t e, uint32_t tk,
+                                                     uint32_t lane, uint8_t* stage) {
   const EncodeArgs& a = p.a;
   const Elem el = a.elems[e];
   const uint32_t t = tk - el.tileBase;
@@ -493,14 +499,11 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
     ans = fbase + kFloatHeaderBytes + floatRawBytes(a.floatType, n);
     if (a.round) ans += *(const uint32_t*)(fbase + 16);
   }
+  constexpr uint32_t kGroupTiles = kGroupBlocks / kTileBlocks; // 32
   const uint32_t firstBlk = t * kTileBlocks;
-  const uint32_t grp = firstBlk / kGroupBlocks;
+  const uint32_t grp = t / kGroupTiles;
   const uint32_t* groupSum = p.groupWords + el.groupBase;
   const uint32_t* bwords = p.blockWords + el.blockBase;
-  uint32_t part = 0;
-  for (uint32_t g = lane; g < grp; g += 32) part += __ldcg(groupSum + g);
-  for (uint32_t b = grp * kGroupBlocks + lane; b < firstBlk; b += 32) part += roundUp(__ldcg(bwords + b), 8);
-  const uint32_t excl = warpSum(part);
   // lane j < 8 owns block firstBlk + j
   const uint32_t myBlk = firstBlk + lane;
   uint32_t words = 0, blkLen = 0;
@@ -508,6 +511,16 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
     words = __ldcg(bwords + myBlk);
     blkLen = min(kBlockSyms, n - myBlk * kBlockSyms);
   }
+  uint32_t part = 0;
+  if (grp * kGroupTiles + lane < t) part = __ldcg(p.tileWords + tk - t + grp * kGroupTiles + lane);
+  for (uint32_t g = lane; g < grp; g += 128) { // 4 loads in flight per lane (a 4 GiB element has 4096 groups)
+    const uint32_t x0 = __ldcg(groupSum + g);
+    const uint32_t x1 = g + 32 < grp ? __ldcg(groupSum + g + 32) : 0u;
+    const uint32_t x2 = g + 64 < grp ? __ldcg(groupSum + g + 64) : 0u;
+    const uint32_t x3 = g + 96 < grp ? __ldcg(groupSum + g + 96) : 0u;
+    part += x0 + x1 + x2 + x3;
+  }
+  const uint32_t excl = warpSum(part);
   const uint32_t padded = roundUp(words, 8);
   uint32_t incl = padded;
 #pragma unroll
@@ -518,31 +531,38 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
   const uint32_t startWord = excl + incl - padded;
   const uint32_t tileWords = __shfl_sync(0xffffffffu, incl, kTileBlocks - 1);
   if (blkLen) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[myBlk] = make_uint2((blkLen << 16) | words, startWord);
-  uint8_t* payload = ans + ansOverhead(nb);
+
+  // ---- payload ----
+  constexpr uint32_t kCap = kEncWarpSmem / 16; // staging capacity in 16-byte vectors
+  const uint32_t stageAddr = smemAddr(stage);
+  uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)excl); // the tile's first vector in the archive
   const uint8_t* slots = p.scratch + (size_t)(el.blockBase + firstBlk) * kSlotBytes;
-  // two blocks at a time, up to two 16-byte vectors per lane and block in flight
+  uint32_t fill = 0;
+  auto drain = [&]() {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+    for (uint32_t i = lane; i < fill; i += 32) dst[i] = ((const uint4*)stage)[i];
+    __syncwarp(); // staging is rewritten next
+    dst += fill;
+    fill = 0;
+  };
 #pragma unroll 1
-  for (uint32_t j = 0; j < kTileBlocks; j += 2) {
-    const uint32_t nvA = __shfl_sync(0xffffffffu, padded, j) >> 3, nvB = __shfl_sync(0xffffffffu, padded, j + 1) >> 3;
-    const uint32_t stA = __shfl_sync(0xffffffffu, startWord, j), stB = __shfl_sync(0xffffffffu, startWord, j + 1);
-    if ((nvA | nvB) == 0) continue;
-    const uint4* srcA = (const uint4*)(slots + (size_t)j * kSlotBytes);
-    const uint4* srcB = (const uint4*)(slots + (size_t)(j + 1) * kSlotBytes);
-    uint4* dstA = (uint4*)(payload + 2 * (size_t)stA);
-    uint4* dstB = (uint4*)(payload + 2 * (size_t)stB);
-    uint4 a0, a1, b0, b1;
-    a0 = a1 = b0 = b1 = make_uint4(0, 0, 0, 0);
-    if (lane < nvA) a0 = __ldcg(srcA + lane);
-    if (lane + 32 < nvA) a1 = __ldcg(srcA + lane + 32);
-    if (lane < nvB) b0 = __ldcg(srcB + lane);
-    if (lane + 32 < nvB) b1 = __ldcg(srcB + lane + 32);
-    if (lane < nvA) dstA[lane] = a0;
-    if (lane + 32 < nvA) dstA[lane + 32] = a1;
-    if (lane < nvB) dstB[lane] = b0;
-    if (lane + 32 < nvB) dstB[lane + 32] = b1;
-    for (uint32_t i = lane + 64; i < nvA; i += 32) dstA[i] = __ldcg(srcA + i);
-    for (uint32_t i = lane + 64; i < nvB; i += 32) dstB[i] = __ldcg(srcB + i);
+  for (uint32_t j = 0; j < kTileBlocks; ++j) {
+    const uint32_t nv = __shfl_sync(0xffffffffu, padded, j) >> 3;
+    if (nv == 0) continue;
+    const uint4* src = (const uint4*)(slots + (size_t)j * kSlotBytes);
+    if (fill + nv > kCap) drain();
+    if (nv > kCap) { // a block larger than the staging area (incompressible data): straight through registers
+      for (uint32_t i = lane; i < nv; i += 32) dst[i] = __ldcg(src + i);
+      dst += nv;
+      continue;
+    }
+    for (uint32_t i = lane; i < nv; i += 32)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(stageAddr + (fill + i) * 16), "l"(src + i) : "memory");
+    fill += nv;
   }
+  if (fill) drain();
+
   if (t == 0) { // pdf table; zero for absent symbols and for an empty element
     const uint2* tab = p.table + (size_t)e * 256;
 #pragma unroll

@@ -128,6 +128,9 @@ int verifyChecksums(Temp& tmp, const Elem* elemsDev, uint32_t num, uint32_t maxU
 }
 
 // ---- ANS ----------------------------------------------------------------------------------
+bool fusedCompressEnabled();
+uint32_t fusedMinTiles();
+
 int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t num, const void* const* in,
               const uint32_t* inSize, const uint32_t* histDev, void* const* out, uint32_t* outSizeDev,
               cudaStream_t s) {
@@ -143,11 +146,12 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   if ((rc = upload(tmp, wl, &elemsDev, s))) return rc;
   uint32_t* checksum = nullptr;
   const uint32_t* hist = histDev;
+  const bool fused = !histDev && wl.totalTiles >= fusedMinTiles() && fusedCompressEnabled(); // histogram, tables, encoding and compaction in one launch
   if (!hist) {
     uint32_t* h = tmp.alloc<uint32_t>((size_t)num * 256);
     if (tmp.failed()) return kErrCuda;
     DGB_CUDA(cudaMemsetAsync(h, 0, (size_t)num * 1024, s));
-    if ((rc = launchHistogram(elemsDev, num, wl.totalTiles, h, s))) return rc;
+    if (!fused && (rc = launchHistogram(elemsDev, num, wl.totalTiles, h, s))) return rc;
     hist = h;
   }
   if (useChecksum) {
@@ -170,6 +174,7 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   a.useChecksum = useChecksum ? 1 : 0;
   EncodeScratch es;
   if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es, s))) return rc;
+  if (fused) return launchFusedCompress(kFtNone, a, es, wl.totalTiles, nullptr, 0, s);
   return launchAnsEncode(a, es, wholeRange(wl, num), s);
 }
 
@@ -225,8 +230,21 @@ cudaStream_t sideStream() {
   return side[dev];
 }
 
-// DGB_FUSED=0 selects the separate split / normalise / encode launches (kept for the sparse and fp64 paths)
+// DGB_FUSED=0 selects the separate split / normalise / encode launches (kept for the sparse and fp64 paths).
+// The fused persistent kernel pays a start-up bubble (encode warps wait for the first element's table) and a
+// compaction tail; measured on B200 it wins from about 1024 8-block tiles (32 MiB of symbols) upwards and loses
+// below (bf16 16 x 1 MiB: 0.068 ms fused vs 0.048 ms as separate launches; 32 x 2 MiB: 0.107 vs 0.112).
 constexpr uint32_t kFusedMinElems = 1;
+static long long g_fusedMinTiles = -1; // < 0: default (or DGB_FUSED_MIN_TILES); set by dgb_set_fused_min_tiles
+uint32_t fusedMinTiles() {
+  if (g_fusedMinTiles >= 0) return (uint32_t)g_fusedMinTiles;
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DGB_FUSED_MIN_TILES"); // experiment knob
+    v = e ? atoi(e) : 1024;
+  }
+  return (uint32_t)v;
+}
 
 bool fusedCompressEnabled() {
   static int on = -1;
@@ -311,8 +329,9 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);
-    if (planes == 1 && !nDev && !denseIn && num >= kFusedMinElems && fusedCompressEnabled())
-      return launchFusedFloatCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
+    if (planes == 1 && !nDev && !denseIn && num >= kFusedMinElems && wl.totalTiles >= fusedMinTiles() &&
+        fusedCompressEnabled())
+      return launchFusedCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
     if ((rc = split(all, s))) return rc;
     for (int r = 0; r < planes; ++r)
       if ((rc = launchAnsEncode(args[r], es[r], all, s))) return rc;
@@ -518,6 +537,8 @@ const char* dgb_version(void) { return "dietgpu_b200 r1 sm_100a"; }
 
 size_t dgb_last_temp_bytes_used(void) { return Temp::lastHighWater(); }
 
+void dgb_set_fused_min_tiles(long long tiles) { g_fusedMinTiles = tiles; }
+
 // dietgpu/ans/GpuANSEncode.cu:13-25: the reference passes the block SIZE (4096) where
 // getCompressedOverhead expects a block COUNT; the value is part of the API (Python sizes and
 // validates buffers with it), so it is reproduced.
@@ -544,7 +565,7 @@ size_t dgb_temp_bytes_required(int op, int ft, uint32_t num, uint32_t maxSize) {
   const size_t spTiles = B * (divUp(maxSize, 8192) + 1);
   const size_t desc = (B + 1) * sizeof(Elem) + 512;
   const size_t blocks = B * (divUp(maxSize, kBlockSyms) + 1);
-  const size_t enc = B * 256 * 8 + tiles * 8 + B * 8 + blocks * (4 + 5632) + 2048; // tables, tile states, scratch slots
+  const size_t enc = B * 256 * 8 + tiles * 8 + B * 32 + blocks * (4 + 5632) + 6144; // tables, control words, scratch slots
   const size_t dec = B * (sizeof(DecInfo) + (4u << 11)) * 2 + 1024;
   const size_t row = roundUpSz(maxSize, 16);
   const size_t wb = floatWordBytes(ft);

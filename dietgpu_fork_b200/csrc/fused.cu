@@ -1,5 +1,5 @@
-// Fused float compress for sm_100a: float split, table normalisation, rANS block encoding of the exponent
-// plane and compaction of the encoded blocks into the archive in ONE persistent launch.
+// Fused compress for sm_100a: float split (or, for the raw ANS codec, the byte histogram), table normalisation,
+// rANS block encoding and compaction of the encoded blocks into the archive in ONE persistent launch.
 //
 // Why: measured on B200 the split is bound by shared-memory atomic throughput and the
 // encoder by instruction issue; run back to back they add up, run on the same SMs at the same time they
@@ -42,7 +42,7 @@ struct FusedParams {
   uint32_t* coalClaim;    // zeroed: next compaction tile to hand out (nullptr: k_coalesce runs as a second launch)
   uint32_t totalTiles;
   uint32_t splitCtasPerSm;
-  unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run start, end, smid/role}
+  unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run end, end, smid/role, encode end}
 };
 
 constexpr uint32_t kFusedThreads = kEncWarps * 32; // 128
@@ -52,13 +52,52 @@ constexpr uint32_t kFusedNormBytes = (256 + 16) * 4;
 constexpr uint32_t kFusedSmem =
     kEncWarps * kEncWarpSmem > kFusedHistBytes + kFusedNormBytes ? kEncWarps * kEncWarpSmem : kFusedHistBytes + kFusedNormBytes;
 
+// Raw ANS (FT == kFtNone): the "split" role only counts bytes; the encode role reads the caller's input.
+// Byte histogram of one 32768-byte tile into the CTA's per-warp replicated bins.
+template <int NT>
+__device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t* sh) {
+  const uint32_t tid = threadIdx.x;
+  uint32_t* wh = sh + (tid >> 5) * 256 * kSplitRep;
+  const uint32_t rep = tid & (kSplitRep - 1);
+  if (off >= n) return;
+  const uint8_t* q = in + off;
+  const uint8_t* end = q + min(kTileSyms, n - off);
+  const uint8_t* a0 = (const uint8_t*)(((uintptr_t)q + 15) & ~(uintptr_t)15);
+  if (a0 > end) a0 = end;
+  const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
+  if (tid < (uint32_t)(a0 - q)) splitHistAdd(wh, q[tid], rep);
+  if (tid >= 32 && tid - 32 < (uint32_t)(end - a1)) splitHistAdd(wh, a1[tid - 32], rep);
+  const uint4* v = (const uint4*)a0;
+  const uint32_t nvec = (uint32_t)(a1 - a0) >> 4;
+  auto addWord = [&](uint32_t x) {
+    splitHistAdd(wh, x & 0xffu, rep);
+    splitHistAdd(wh, (x >> 8) & 0xffu, rep);
+    splitHistAdd(wh, (x >> 16) & 0xffu, rep);
+    splitHistAdd(wh, x >> 24, rep);
+  };
+  uint32_t i = tid;
+  for (; i + 3 * NT < nvec; i += 4 * NT) {
+    uint4 x[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) x[k] = __ldg(v + i + NT * k);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      addWord(x[k].x); addWord(x[k].y); addWord(x[k].z); addWord(x[k].w);
+    }
+  }
+  for (; i < nvec; i += NT) {
+    const uint4 x = __ldg(v + i);
+    addWord(x.x); addWord(x.y); addWord(x.z); addWord(x.w);
+  }
+}
+
 template <int FT, int PB>
 __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(const __grid_constant__ FusedParams p) {
-  static_assert(FloatTraits<FT>::kPlanes == 1, "single exponent plane only");
+  if constexpr (FT != kFtNone) static_assert(FloatTraits<FT>::kPlanes == 1, "single exponent plane only");
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint32_t sBcast[2];
   const uint32_t tid = threadIdx.x;
-  unsigned long long t0 = 0, t1 = 0, t2 = 0;
+  unsigned long long t0 = 0, t1 = 0, t2 = 0, tEnc = 0;
   uint32_t smidTrace = 0;
   if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
 
@@ -93,7 +132,12 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
         const uint32_t elemEnd = p.sp.elems[e + 1].tileBase;
         const uint32_t stop = min(last, elemEnd);
         const uint32_t count = stop - tile;
-        for (; tile < stop; ++tile) splitTile<FT, kFusedThreads>(p.sp, e, el, n, tile, sh);
+        for (; tile < stop; ++tile) {
+          if constexpr (FT == kFtNone)
+            histTileBytes<kFusedThreads>((const uint8_t*)el.in, n, (tile - el.tileBase) * kTileSyms, sh);
+          else
+            splitTile<FT, kFusedThreads>(p.sp, e, el, n, tile, sh);
+        }
         __syncthreads();
         splitHistFlush<kFusedThreads>(sh, p.sp.hist0 + (size_t)e * 256, tid);
         __threadfence(); // plane, raw bytes and histogram of these tiles before the tile count
@@ -135,6 +179,7 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     }
     run = __shfl_sync(0xffffffffu, nextRun, 0);
   }
+  if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tEnc));
   // Compaction: warps that ran out of runs take tickets for 8-block tiles in order and wait until the tile's
   // element is completely encoded. Every run is by now owned by a running warp that waits for nothing but split
   // CTAs, so the wait cannot deadlock; elements finish in order, so early finishers find work immediately.
@@ -149,18 +194,23 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
       guess = ce;
       if (w.lane == 0) {
         const uint32_t want = (p.sp.elems[ce + 1].tileBase - p.sp.elems[ce].tileBase) << p.ep.runShift;
-        while (ldRelaxed(p.runsDone + ce) != want) __nanosleep(200);
+        uint32_t ns = 250; // growing back-off: thousands of warps may wait for the same element
+        while (ldRelaxed(p.runsDone + ce) != want) {
+          __nanosleep(ns);
+          if (ns < 2000) ns *= 2;
+        }
         (void)ldAcquire(p.runsDone + ce);
       }
       __syncwarp();
-      coalesceTileWarp(p.ep, PB, ce, tk, w.lane);
+      coalesceTileWarp(p.ep, PB, ce, tk, w.lane, w.tabSmem);
     }
   }
   if (p.trace && tid == 0) {
     unsigned long long t3;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t3));
-    unsigned long long* r = p.trace + 5ull * blockIdx.x;
+    unsigned long long* r = p.trace + 6ull * blockIdx.x;
     r[0] = t0; r[1] = t1; r[2] = t2; r[3] = t3; r[4] = ((unsigned long long)smidTrace << 1) | (splitRole ? 1u : 0u);
+    r[5] = tEnc;
   }
 }
 
@@ -184,20 +234,21 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   const uint32_t grid = min(want, (uint32_t)smCount() * (uint32_t)perSm);
   static const char* tracePath = getenv("DGB_FUSED_TRACE"); // debugging aid: per-CTA timeline of the last launch
   p.trace = nullptr;
-  if (tracePath) DGB_CUDA(cudaMalloc(&p.trace, 5ull * 8 * grid));
+  if (tracePath) DGB_CUDA(cudaMalloc(&p.trace, 6ull * 8 * grid));
   {
     ProfScope ps__("k_compressFused", s);
     kern<<<grid, kFusedThreads, kFusedSmem, s>>>(p);
   }
   DGB_CUDA(cudaGetLastError());
   if (tracePath) {
-    std::vector<unsigned long long> h(5ull * grid);
+    std::vector<unsigned long long> h(6ull * grid);
     DGB_CUDA(cudaMemcpyAsync(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost, s));
     DGB_CUDA(cudaStreamSynchronize(s));
     cudaFree(p.trace);
     if (FILE* f = fopen(tracePath, "w")) {
       for (uint32_t i = 0; i < grid; ++i)
-        fprintf(f, "%u %llu %llu %llu %llu %llu\n", i, h[5 * i], h[5 * i + 1], h[5 * i + 2], h[5 * i + 3], h[5 * i + 4]);
+        fprintf(f, "%u %llu %llu %llu %llu %llu %llu\n", i, h[6 * i], h[6 * i + 1], h[6 * i + 2], h[6 * i + 3], h[6 * i + 4],
+                h[6 * i + 5]);
       fclose(f);
     }
   }
@@ -213,7 +264,7 @@ static int launchFusedPb(FusedParams& p, int pb, cudaStream_t s) {
   }
 }
 
-int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
+int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
                              const uint32_t* checksum, int useChecksum, cudaStream_t s) {
   if (a.numElems == 0) return kOk;
   if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
@@ -239,12 +290,14 @@ int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& e
   p.tilesDone = es.fusedCtrl + kFusedCtrlFixed;
   p.ready = p.tilesDone + a.numElems;
   p.runsDone = p.ready + a.numElems;
+  p.ep.tileWords = p.runsDone + a.numElems;
   static const bool separateCoalesce = getenv("DGB_FUSED_COALESCE") && atoi(getenv("DGB_FUSED_COALESCE")) == 0;
   p.coalClaim = separateCoalesce ? nullptr : es.fusedCtrl + kFusedCtrlFixed - 1; // experiment knob
   p.ep.ready = p.ready;
   p.totalTiles = totalTiles;
   int rc;
   switch (ft) {
+    case kFtNone: rc = launchFusedPb<kFtNone>(p, a.probBits, s); break;
     case kFtF16: rc = launchFusedPb<kFtF16>(p, a.probBits, s); break;
     case kFtBF16: rc = launchFusedPb<kFtBF16>(p, a.probBits, s); break;
     case kFtF32: rc = launchFusedPb<kFtF32>(p, a.probBits, s); break;

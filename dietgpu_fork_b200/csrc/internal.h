@@ -142,7 +142,7 @@ struct EncodeScratch {
   uint32_t* blockWords;
   uint32_t* groupWords;
   uint32_t* runCounters;
-  uint32_t* fusedCtrl; // [kFusedCtrlFixed + 3 * numElems]: split counter, SM tickets, compaction claims | tilesDone | ready | runsDone
+  uint32_t* fusedCtrl; // [kFusedCtrlFixed + 3 * numElems + tiles]: split counter, SM tickets, compaction claims | tilesDone | ready | runsDone | tileWords
   uint8_t* scratch;
 };
 // totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
@@ -151,9 +151,9 @@ int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, Enc
 int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
 // compaction only (k_coalesce), for callers that produced the block slots themselves
 int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
-// float split + table normalisation + block encoding + compaction of one exponent plane in ONE persistent
-// launch. Single-plane float types, host-known sizes, dense input (fused.cu).
-int launchFusedFloatCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
+// float split (ft == kFtNone: byte histogram of the raw input) + table normalisation + block encoding +
+// compaction in ONE persistent launch. Single-plane float types or raw ANS, host-known sizes, dense input (fused.cu).
+int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
                              const uint32_t* checksum, int useChecksum, cudaStream_t s);
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or

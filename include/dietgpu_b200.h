@@ -152,6 +152,14 @@ int dgb_float_get_compressed_info(const void* const* in, int in_is_device, uint3
  * dietgpu/utils/StackDeviceMemory.h:196-200. */
 size_t dgb_last_temp_bytes_used(void);
 
+/* ---- tuning ----------------------------------------------------------------------------------- */
+/* Compress chooses between two bit-identical schedules: one persistent fused launch (split or byte
+ * histogram + table + encode + compaction) for batches of at least `tiles` 8-block tiles (32768 symbols
+ * each), separate launches below. Default 1024 (measured cross-over on B200); 0 = always fused,
+ * a huge value = never, negative = back to the default. Process-wide; used by the parity tests to
+ * cover both schedules at every size. */
+void dgb_set_fused_min_tiles(long long tiles);
+
 /* ---- launch accounting (bench.py) --------------------------------------------------------- */
 /* Total kernel launches the library has enqueued in this process. */
 unsigned long long dgb_profile_launches(void);

@@ -1,7 +1,7 @@
 """Device-resident throughput of every BASELINE.json config, ours next to the reference's CUDA build (when
 oracle/_ref/libdietgpu_ref.so exists) with the identical harness: same buffers, CUDA events on the current stream,
 3 warm-ups, N timed calls, compressed outputs compared byte-count for byte-count. One JSON line per config.
-Usage: python scripts/bench_configs.py [--steps 10] [--only ans,bf16,f32_1g,f32_64,f16,f64,sparse]"""
+Usage: python scripts/bench_configs.py [--steps 10] [--only ans,bf16,f32_1g,f32_64,f16,f64,sparse[,bf16_small,bf16_tiny,ans_big]]"""
 import argparse
 import ctypes as C
 import json
@@ -139,6 +139,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--only", default="")
+    ap.add_argument("--custom", default="", help="comma list of bf16:<batch>:<KiB per element> (e.g. bf16:32:2048)")
     a = ap.parse_args()
     only = set(a.only.split(",")) if a.only else None
     torch.cuda.set_device(0)
@@ -170,6 +171,28 @@ def main():
         g.manual_seed(3000)
         ins = [torch.randn(1 << 22, device="cuda", generator=g) for _ in range(64)]
         run_config("fp32 64 x 16 MiB N(0,1)", "float", codec.FLOAT32, ins, [1 << 22] * 64, a.steps)
+    # opt-in extras (only with --only): small batches (launch/latency bound) and a large raw-ANS batch
+    if only and "bf16_small" in only:
+        g.manual_seed(2002)
+        ins = [(torch.randn(1 << 19, device="cuda", generator=g) * 0.02).to(torch.bfloat16) for _ in range(16)]
+        run_config("bf16 16 x 1 MiB N(0,0.02)", "float", codec.BFLOAT16, ins, [1 << 19] * 16, a.steps)
+    if only and "bf16_tiny" in only:
+        g.manual_seed(2003)
+        ins = [(torch.randn(1 << 17, device="cuda", generator=g) * 0.02).to(torch.bfloat16) for _ in range(4)]
+        run_config("bf16 4 x 256 KiB N(0,0.02)", "float", codec.BFLOAT16, ins, [1 << 17] * 4, a.steps)
+    if only and "ans_big" in only:
+        g.manual_seed(1001)
+        ins = [torch.clamp(torch.floor(256 * torch.clamp(-torch.log(torch.rand(1 << 22, device="cuda", generator=g)) / 20.0,
+                                                         max=1.0)), max=255).to(torch.uint8) for _ in range(128)]
+        run_config("ANS bytes 128 x 4 MiB lambda=20", "ans", 0, ins, [1 << 22] * 128, a.steps)
+    for spec in [c for c in a.custom.split(",") if c]:
+        kind, b, kib = spec.split(":")
+        b, words = int(b), int(kib) * 512
+        g.manual_seed(2004)
+        ins = [(torch.randn(words, device="cuda", generator=g) * 0.02).to(torch.bfloat16) for _ in range(b)]
+        run_config(f"bf16 {b} x {kib} KiB N(0,0.02)", "float", codec.BFLOAT16, ins, [words] * b, a.steps)
+    if a.custom and not a.only:
+        return
     if want("f64"):  # config 4
         g.manual_seed(4000)
         ins = [torch.randn(1 << 20, device="cuda", generator=g, dtype=torch.float64) for _ in range(16)]

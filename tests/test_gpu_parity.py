@@ -16,6 +16,16 @@ F16, BF16, F32, F64 = 1, 2, 3, 4
 needs_ref = pytest.mark.skipif(H.ref_lib() is None, reason="oracle/_ref/libdietgpu_ref.so not built")
 
 
+@pytest.fixture(autouse=True, params=["fused", "separate"])
+def compress_schedule(request):
+    """Every test runs under both compress schedules (one persistent fused launch / separate launches);
+    without this the size threshold would keep the fused kernel away from the small parity cases."""
+    from dietgpu_fork_b200 import _capi
+    _capi.lib.dgb_set_fused_min_tiles(0 if request.param == "fused" else 1 << 40)
+    yield request.param
+    _capi.lib.dgb_set_fused_min_tiles(-1)
+
+
 def _assert_same(ours, expect, what):
     assert ours.size == expect.size, f"{what}: size {ours.size} != {expect.size}"
     if not np.array_equal(ours, expect):
