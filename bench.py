@@ -8,9 +8,9 @@ batch of the same shape (independent batch elements sharded across ranks, no dat
 
   value      (U_compress + U_decompress) / t  in GB/s of UNCOMPRESSED bytes, inputs resident in HBM,
              summed over ranks; t = device time (CUDA events), max over ranks.
-  e2e        same metric through the torch-op mirror (compress_data / decompress_data) with HOST
-             buffers: pinned H2D of the batch and D2H of the decompressed batch + sizes inside the
-             timed region.
+  e2e        same metric with HOST buffers through the C ABI's host-buffer calls
+             (dgb_float_compress_host / dgb_float_decompress_host): tensors and archives live in pinned
+             host memory, every H2D / D2H copy is inside the timed region (see run_e2e).
   roofline   the dominant kernel (largest share of device time), its algorithmic bytes per launch
              over its event-timed duration, against MEASURED_PEAKS.json's hbm_gbs.
   cpu_baseline  the CPU oracle (a port of the same stream format; the reference has NO CPU codec)
@@ -370,49 +370,92 @@ def main():
 
 
 def run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks):
-    """compress_data / decompress_data with pinned HOST buffers in the timed region."""
-    from dietgpu_fork_b200 import torch_ops
+    """The same step with HOST buffers: pinned host tensors in, archives in pinned host memory, decompressed
+    tensors back in pinned host memory; every host<->device copy is inside the timed region.
+
+    ours       codec.float_compress_host + codec.float_decompress_host: the C ABI's host-buffer entry points,
+               which pipeline H2D / kernels / D2H over element groups inside the library (csrc/host_pipe.cu).
+    reference  its API takes device pointers only, so the caller does what its users do: copy the batch in,
+               floatCompress, read the sizes, copy the archives out (exact sizes); copy them back in,
+               floatDecompress, copy the tensors out.
+    `unpipelined` is that same plain sequence around OUR device-pointer calls, to separate what the pipelining
+    buys from what the kernels buy (PCIe dominates both)."""
+    from dietgpu_fork_b200 import codec
     U = BATCH * ELEM_WORDS * 2
+    max_bytes = comp.shape[1]
     host_in = torch.empty((BATCH, ELEM_WORDS), dtype=torch.bfloat16).pin_memory()
     host_out = torch.empty((BATCH, ELEM_WORDS), dtype=torch.bfloat16).pin_memory()
+    host_comp = torch.empty((BATCH, max_bytes), dtype=torch.uint8).pin_memory()
     for i in range(BATCH):
         host_in[i].copy_(ins[i])
+    hin_rows = [host_in[i] for i in range(BATCH)]
+    hout_rows = [host_out[i] for i in range(BATCH)]
+    hcomp_rows = [host_comp[i] for i in range(BATCH)]
     dev_in = torch.empty((BATCH, ELEM_WORDS), dtype=torch.bfloat16, device="cuda")
     dev_out = torch.empty((BATCH, ELEM_WORDS), dtype=torch.bfloat16, device="cuda")
     in_rows = [dev_in[i] for i in range(BATCH)]
     out_rows = [dev_out[i] for i in range(BATCH)]
+    comp2 = torch.empty_like(comp)  # the archives come back in from the host into a second device buffer
+    rows2 = [comp2[i] for i in range(BATCH)]
+    copied = {"h2d": 0, "d2h": 0}
 
-    def step():
+    def plain_step(compress, decompress):
         dev_in.copy_(host_in, non_blocking=True)
-        if ref is not None:
-            ref.compress(in_rows, rows, sizes)
-            ref.decompress(rows, out_rows, ok, dsizes)
-        else:
-            torch_ops.compress_data(True, in_rows, False, temp, comp, sizes)
-            torch_ops.decompress_data(True, rows, out_rows, False, temp, ok, dsizes)
+        compress(in_rows, rows, sizes)
+        csz = sizes.cpu().tolist()  # blocks: archive sizes exist only on the device
+        for i, n in enumerate(csz):
+            host_comp[i, :n].copy_(comp[i, :n], non_blocking=True)
+        for i, n in enumerate(csz):
+            comp2[i, :n].copy_(host_comp[i, :n], non_blocking=True)
+        decompress(rows2, out_rows, ok, dsizes)
         host_out.copy_(dev_out, non_blocking=True)
-        return sizes.cpu()  # blocks: the caller learns the compressed sizes
+        torch.cuda.synchronize()
+        c = sum(csz)
+        copied["h2d"], copied["d2h"] = U + c, c + U + BATCH * 4
+
+    def pipelined_step():
+        csz = codec.float_compress_host(BF16, hin_rows, hcomp_rows, 10, False)
+        codec.float_decompress_host(BF16, hcomp_rows, csz, hout_rows, 10, False)
+        c = sum(csz)
+        copied["h2d"], copied["d2h"] = U + c, c + U + 2 * BATCH * 4 + BATCH
+
+    def timed(step, steps):
+        step()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        host_out.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            step()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        assert torch.equal(host_out.view(torch.int16), host_in.view(torch.int16)), "e2e round trip mismatch"
+        return n_ranks * 2.0 * U / (ms / steps * 1e-3) / 1e9
 
     steps = max(2, min(args.steps, 5))
-    step()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(steps):
-        step()
-    b.record()
-    torch.cuda.synchronize()
-    ms = a.elapsed_time(b)
-    if dist is not None:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = t.item()
-    assert torch.equal(host_out.view(torch.int16), host_in.view(torch.int16)), "e2e round trip mismatch"
-    return {"value": round(n_ranks * 2.0 * U / (ms / steps * 1e-3) / 1e9, 2), "unit": "GB/s",
-            "h2d_bytes_per_step": U, "d2h_bytes_per_step": U + BATCH * 4, "steps": steps}
+    if ref is not None:
+        v = timed(lambda: plain_step(ref.compress, ref.decompress), steps)
+        return {"value": round(v, 2), "unit": "GB/s", "h2d_bytes_per_step": copied["h2d"],
+                "d2h_bytes_per_step": copied["d2h"], "steps": steps,
+                "path": "H2D, floatCompress, sizes D2H, archives D2H, archives H2D, floatDecompress, D2H "
+                        "(the reference API takes device pointers only)"}
+    plain = timed(lambda: plain_step(
+        lambda i, o, s: codec.float_compress(BF16, i, o, s, 10, False, temp=temp),
+        lambda i, o, k, s: codec.float_decompress(BF16, i, o, k, s, 10, False, temp=temp)), steps)
+    v = timed(pipelined_step, steps)
+    return {"value": round(v, 2), "unit": "GB/s", "h2d_bytes_per_step": copied["h2d"],
+            "d2h_bytes_per_step": copied["d2h"], "steps": steps,
+            "path": "dgb_float_compress_host + dgb_float_decompress_host (copies and kernels pipelined over "
+                    "element groups inside the call)",
+            "unpipelined": round(plain, 2)}
 
 
 def reference_cpu_arm(args):

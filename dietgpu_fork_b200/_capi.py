@@ -54,6 +54,11 @@ def _load():
     L.dgb_float_decompress_split_size.argtypes = f_tail + [vp, vp, vp, vp, vp, vp] + mm
     L.dgb_float_decompress_sparse.argtypes = f_tail + [vp, vp, vp, vp, vp, vp]
     L.dgb_float_get_compressed_info.argtypes = [vp, i, u32, vp, vp, vp, vp, sz, vp]
+    L.dgb_float_compress_host.argtypes = [i, i, i, u32, vp, vp, vp, vp, vp, vp]
+    L.dgb_float_decompress_host.argtypes = [i, i, i, u32, vp, vp, vp, vp, vp, vp, vp]
+    L.dgb_ans_encode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp]
+    L.dgb_ans_decode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp, vp]
+    L.dgb_host_release.restype = None
     L.dgb_profile_launches.restype = C.c_ulonglong
     L.dgb_profile_enable.argtypes = [i]
     L.dgb_set_fused_min_tiles.argtypes = [C.c_longlong]
@@ -65,7 +70,8 @@ def _load():
                  "dgb_ans_decode_batch_stride", "dgb_ans_decode_batch_split_size",
                  "dgb_ans_get_compressed_info", "dgb_float_compress", "dgb_float_compress_split_size",
                  "dgb_float_compress_sparse", "dgb_float_decompress", "dgb_float_decompress_split_size",
-                 "dgb_float_decompress_sparse", "dgb_float_get_compressed_info"):
+                 "dgb_float_decompress_sparse", "dgb_float_get_compressed_info", "dgb_float_compress_host",
+                 "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host"):
         getattr(L, name).restype = i
     return L
 
@@ -82,6 +88,8 @@ EXPORTS = [
     "dgb_ans_decode_batch_split_size", "dgb_ans_get_compressed_info", "dgb_float_compress",
     "dgb_float_compress_split_size", "dgb_float_compress_sparse", "dgb_float_decompress",
     "dgb_float_decompress_split_size", "dgb_float_decompress_sparse", "dgb_float_get_compressed_info",
+    "dgb_float_compress_host", "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host",
+    "dgb_host_release",
 ]
 
 

@@ -151,3 +151,69 @@ def float_get_compressed_info(ins, out_sizes=None, out_types=None, out_checksum=
     rc = lib.dgb_float_get_compressed_info(_ptrs(ins), 0, len(ins), _ptr(out_sizes), _ptr(out_types),
                                            _ptr(out_checksum), None, 0, _stream(stream))
     _capi.check(rc, "floatGetCompressedInfo")
+
+
+# ---- host buffers (include/dietgpu_b200.h "host buffers", csrc/host_pipe.cu) ------------------------------
+# CPU tensors in, CPU tensors out: the copies, the codec kernels and the size read-back are pipelined over
+# groups of batch elements inside the library. Pinned tensors let the copies overlap; pageable ones work.
+def _host_ptrs(ts):
+    for t in ts:
+        assert not t.is_cuda and t.is_contiguous(), "host-buffer calls take contiguous CPU tensors"
+    return _capi.ptr_array([t.data_ptr() for t in ts])
+
+
+def float_compress_host(float_type, ins, outs, prob_bits=10, use_checksum=False, stream=None, in_sizes=None):
+    """Compresses the CPU tensors `ins` (float words) into the CPU byte tensors `outs`; returns the archive
+    sizes in bytes (list of int). Archives are byte-identical to float_compress'."""
+    n = len(ins)
+    sizes = in_sizes if in_sizes is not None else [t.numel() for t in ins]
+    caps = [t.numel() * t.element_size() for t in outs]
+    out_sizes = (C.c_uint32 * max(n, 1))()
+    rc = lib.dgb_float_compress_host(float_type, prob_bits, int(use_checksum), n, _host_ptrs(ins),
+                                     _capi.u32_array(sizes), _host_ptrs(outs), _capi.u32_array(caps), out_sizes,
+                                     _stream(stream))
+    _capi.check(rc, "floatCompress (host buffers)")
+    return list(out_sizes[:n])
+
+
+def float_decompress_host(float_type, ins, in_bytes, outs, prob_bits=10, use_checksum=False, stream=None,
+                          out_capacity=None):
+    """Decompresses the CPU archives `ins` (`in_bytes[i]` bytes each) into the CPU tensors `outs`; returns
+    (success flags, decoded sizes in words)."""
+    n = len(ins)
+    caps = out_capacity if out_capacity is not None else [t.numel() for t in outs]
+    ok = (C.c_uint8 * max(n, 1))()
+    out_sizes = (C.c_uint32 * max(n, 1))()
+    rc = lib.dgb_float_decompress_host(float_type, prob_bits, int(use_checksum), n, _host_ptrs(ins),
+                                       _capi.u32_array(in_bytes), _host_ptrs(outs), _capi.u32_array(caps), ok,
+                                       out_sizes, _stream(stream))
+    if _capi.check(rc, "floatDecompress (host buffers)"):
+        raise ChecksumMismatch([])
+    return list(ok[:n]), list(out_sizes[:n])
+
+
+def ans_encode_host(ins, outs, prob_bits=10, use_checksum=False, stream=None, in_sizes=None):
+    n = len(ins)
+    sizes = in_sizes if in_sizes is not None else [t.numel() * t.element_size() for t in ins]
+    caps = [t.numel() * t.element_size() for t in outs]
+    out_sizes = (C.c_uint32 * max(n, 1))()
+    rc = lib.dgb_ans_encode_host(prob_bits, int(use_checksum), n, _host_ptrs(ins), _capi.u32_array(sizes),
+                                 _host_ptrs(outs), _capi.u32_array(caps), out_sizes, _stream(stream))
+    _capi.check(rc, "ansEncodeBatchPointer (host buffers)")
+    return list(out_sizes[:n])
+
+
+def ans_decode_host(ins, in_bytes, outs, prob_bits=10, use_checksum=False, stream=None, out_capacity=None):
+    n = len(ins)
+    caps = out_capacity if out_capacity is not None else [t.numel() * t.element_size() for t in outs]
+    ok = (C.c_uint8 * max(n, 1))()
+    out_sizes = (C.c_uint32 * max(n, 1))()
+    rc = lib.dgb_ans_decode_host(prob_bits, int(use_checksum), n, _host_ptrs(ins), _capi.u32_array(in_bytes),
+                                 _host_ptrs(outs), _capi.u32_array(caps), ok, out_sizes, _stream(stream))
+    if _capi.check(rc, "ansDecodeBatchPointer (host buffers)"):
+        raise ChecksumMismatch([])
+    return list(ok[:n]), list(out_sizes[:n])
+
+
+def host_release():
+    lib.dgb_host_release()

@@ -147,6 +147,35 @@ int dgb_float_get_compressed_info(const void* const* in, int in_is_device, uint3
                                   uint32_t* out_checksum_dev, void* temp_dev, size_t temp_bytes,
                                   void* stream);
 
+/* ---- host buffers ---------------------------------------------------------------------------- */
+/* The reference's API takes device pointers only; a caller whose tensors live in HOST memory wraps it in
+ * cudaMemcpy in / call / cudaMemcpy the sizes / cudaMemcpy out. These entry points are that sequence as one
+ * call, pipelined over groups of batch elements on three internal streams with their own device staging, so
+ * that the host-to-device copy of one group, the codec kernels of the next and the device-to-host copy of a
+ * third overlap (PCIe is full duplex; csrc/host_pipe.cu). Archives are byte-identical to the device calls'.
+ *   - every pointer is a HOST pointer (pinned memory for the copies to overlap; pageable works, serialised);
+ *   - in_size / out_capacity of the float calls are WORDS, of the ANS calls BYTES; archive sizes are bytes;
+ *   - compress: out_capacity (nullable) = bytes available at out[i]; an archive that does not fit is not
+ *     copied, its size is still reported and the call returns DGB_ERR_INVALID_ARG;
+ *   - decompress: in_bytes[i] = size of archive i as reported by compress;
+ *   - the calls are ordered after the work already enqueued on `stream` and return when every result is in
+ *     host memory. Device staging is cached per device until dgb_host_release(). */
+int dgb_float_compress_host(int float_type, int prob_bits, int use_checksum, uint32_t num_in_batch,
+                            const void* const* in, const uint32_t* in_size, void* const* out,
+                            const uint32_t* out_capacity, uint32_t* out_size, void* stream);
+int dgb_float_decompress_host(int float_type, int prob_bits, int use_checksum, uint32_t num_in_batch,
+                              const void* const* in, const uint32_t* in_bytes, void* const* out,
+                              const uint32_t* out_capacity, uint8_t* out_success, uint32_t* out_size,
+                              void* stream);
+int dgb_ans_encode_host(int prob_bits, int use_checksum, uint32_t num_in_batch, const void* const* in,
+                        const uint32_t* in_size, void* const* out, const uint32_t* out_capacity,
+                        uint32_t* out_size, void* stream);
+int dgb_ans_decode_host(int prob_bits, int use_checksum, uint32_t num_in_batch, const void* const* in,
+                        const uint32_t* in_bytes, void* const* out, const uint32_t* out_capacity,
+                        uint8_t* out_success, uint32_t* out_size, void* stream);
+/* Frees the cached staging buffers and streams of the host-buffer calls (all devices). */
+void dgb_host_release(void);
+
 /* Scratch bytes the last finished call on this thread took (from temp_dev plus the pool): what the
  * reference reports through StackDeviceMemory::getMaxMemoryUsage(),
  * dietgpu/utils/StackDeviceMemory.h:196-200. */
