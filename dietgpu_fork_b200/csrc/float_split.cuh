@@ -77,11 +77,12 @@ __device__ __forceinline__ void splitHistGroup(uint32_t* wh0, uint32_t* wh1, con
   }
 }
 
-// One tile of element e (el = elems[e], n = its word count) by the NT threads of the CTA. sh: the CTA's
-// histogram bins (kPlanes * splitHistWords<NT>() words, zeroed by the caller).
+// One tile of element e (el = elems[e], n = its word count) by the NT threads of the CTA, or the slice
+// [slice * sliceWords, (slice + 1) * sliceWords) of it (sliceWords: a power of two dividing the tile). sh: the
+// CTA's histogram bins (kPlanes * splitHistWords<NT>() words, zeroed by the caller).
 template <int FT, int NT, bool PIPE = true>
 __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, const Elem& el, uint32_t n, uint32_t tile,
-                                          uint32_t* sh) {
+                                          uint32_t* sh, uint32_t sliceWords = kTileSyms, uint32_t slice = 0) {
   using Tr = FloatTraits<FT>;
   using Word = typename Tr::Word;
   constexpr uint32_t G = Tr::kGroup;
@@ -91,9 +92,10 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
   uint32_t* wh1 = wh0 + splitHistWords<NT>();
   const uint32_t rep = tid & (kSplitRep - 1);
   const uint32_t t = tile - el.tileBase;
-  const uint32_t off = t * kTileSyms;
+  const uint32_t sliceOff = slice * sliceWords;
+  const uint32_t off = t * kTileSyms + sliceOff;
   uint8_t* fbase = (uint8_t*)el.out + el.sizeBias;
-  if (t == 0 && tid == 0) {
+  if (t == 0 && slice == 0 && tid == 0) {
     // GpuFloatHeader + GpuFloatHeader2 (dietgpu/float/GpuFloatUtils.cuh:19-96); the second
     // header's firstCompSegmentBytes is filled in by the encoder
     uint32_t cs = (p.useChecksum && p.checksum) ? p.checksum[e] : 0u;
@@ -101,7 +103,7 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     ((uint4*)fbase)[1] = make_uint4(0u, 0u, 0u, 0u);
   }
   if (off >= n) return;
-  const uint32_t len = min(kTileSyms, n - off);
+  const uint32_t len = min(sliceWords, n - off);
   const uint8_t* in = p.denseIn ? p.denseIn + el.planeOff * sizeof(Word) : (const uint8_t*)el.in;
   uint8_t* plane0 = p.plane0 + el.planeOff;
   uint8_t* plane1 = kPlanes == 2 ? p.plane1 + el.planeOff : plane0;

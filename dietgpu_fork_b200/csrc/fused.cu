@@ -7,10 +7,13 @@
 // one grid:
 //   * every CTA draws a per-SM ticket; the first `splitCtasPerSm` CTAs of each SM take the split role, the rest
 //     the encode role, so every SM runs both kinds of work side by side;
-//   * split CTAs claim 32768-word tiles in order from an atomic counter (element-major, so elements complete
-//     one after the other), write raw bytes into the archive and exponent bytes into the plane, and add their
-//     histogram to the element's global bins; the CTA that completes an element's last tile normalises its
-//     table and publishes the element's ready flag (release);
+//   * split CTAs claim work in order from an atomic counter (element-major, so elements complete one after the
+//     other): two 32768-word tiles per claim for batches of many elements, 4096-word slices for a few huge
+//     elements (all CTAs then sweep one contiguous front through memory, and all but one CTA per SM split,
+//     because nothing can be encoded before the first table exists). They write raw bytes into the archive and
+//     exponent bytes into the plane; the histogram stays in the CTA's shared-memory bins while its claims stay
+//     inside one element and is added to the element's global bins when the CTA moves on; the CTA whose slice
+//     count completes an element normalises its table and publishes the element's ready flag (release);
 //   * encode warps claim runs of 4 blocks in the same order, wait (acquire) for the run's element, and encode
 //     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
 //   * a split CTA that finds no tile left becomes an encode CTA;
@@ -42,11 +45,12 @@ struct FusedParams {
   uint32_t* coalClaim;    // zeroed: next compaction tile to hand out (nullptr: k_coalesce runs as a second launch)
   uint32_t totalTiles;
   uint32_t splitCtasPerSm;
+  uint32_t sliceShift; // log2(slices per tile) the split role claims work in
+  uint32_t splitClaim; // slices per claim
   unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run end, end, smid/role, encode end}
 };
 
 constexpr uint32_t kFusedThreads = kEncWarps * 32; // 128
-constexpr uint32_t kSplitClaim = 2;                // tiles a split CTA claims at a time
 constexpr uint32_t kFusedHistBytes = splitHistWords<kFusedThreads>() * 4;
 constexpr uint32_t kFusedNormBytes = (256 + 16) * 4;
 constexpr uint32_t kFusedSmem =
@@ -55,13 +59,14 @@ constexpr uint32_t kFusedSmem =
 // Raw ANS (FT == kFtNone): the "split" role only counts bytes; the encode role reads the caller's input.
 // Byte histogram of one 32768-byte tile into the CTA's per-warp replicated bins.
 template <int NT>
-__device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t* sh) {
+__device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t sliceBytes,
+                                              uint32_t* sh) {
   const uint32_t tid = threadIdx.x;
   uint32_t* wh = sh + (tid >> 5) * 256 * kSplitRep;
   const uint32_t rep = tid & (kSplitRep - 1);
   if (off >= n) return;
   const uint8_t* q = in + off;
-  const uint8_t* end = q + min(kTileSyms, n - off);
+  const uint8_t* end = q + min(sliceBytes, n - off);
   const uint8_t* a0 = (const uint8_t*)(((uintptr_t)q + 15) & ~(uintptr_t)15);
   if (a0 > end) a0 = end;
   const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
@@ -115,48 +120,64 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     uint32_t* sh = (uint32_t*)smem;
     uint32_t* normSm = (uint32_t*)(smem + kFusedHistBytes);
     for (uint32_t i = tid; i < kFusedHistBytes / 4; i += kFusedThreads) sh[i] = 0;
-    uint32_t guess = 0;
+    // Work is claimed in order, in slices of a tile (p.sliceShift: log2 slices per tile). Counts stay in the CTA's
+    // bins while its claims stay inside one element; they go to the element's global bins, followed by the
+    // CTA's slice count, when the CTA moves on. The CTA whose count completes the element owns its table.
+    const uint32_t sliceShift = p.sliceShift, sliceWords = kTileSyms >> sliceShift;
+    const uint32_t totalSlices = p.totalTiles << sliceShift;
+    uint32_t guess = 0, accElem = 0xffffffffu, accSlices = 0;
+    auto publish = [&]() { // all threads
+      __syncthreads();
+      splitHistFlush<kFusedThreads>(sh, p.sp.hist0 + (size_t)accElem * 256, tid);
+      __threadfence(); // plane, raw bytes and histogram of these slices before the slice count
+      __syncthreads();
+      if (tid == 0) {
+        const uint32_t want = (p.sp.elems[accElem + 1].tileBase - p.sp.elems[accElem].tileBase) << sliceShift;
+        const uint32_t done = atomicAdd(&p.tilesDone[accElem], accSlices) + accSlices;
+        sBcast[1] = done == want ? 1u : 0u;
+      }
+      __syncthreads();
+      if (sBcast[1]) { // this CTA completed the element: its histogram is final
+        __threadfence();
+        normalizeElement<kFusedThreads>(p.sp.hist0 + (size_t)accElem * 256, p.sp.elems[accElem].n, PB,
+                                        p.ep.table + (size_t)accElem * 256, normSm);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) stRelease(p.ready + accElem, 1u);
+      }
+      __syncthreads(); // sBcast is rewritten after this point
+      accSlices = 0;
+    };
+    // the next claim is requested before the current one is processed (thread 0 holds the ticket in a register)
+    uint32_t ticket = 0;
+    if (tid == 0) ticket = atomicAdd(p.splitCounter, p.splitClaim);
     for (;;) {
-      // claim kSplitClaim consecutive tiles; histogram flush, fence and tile count once per element touched
-      if (tid == 0) sBcast[0] = atomicAdd(p.splitCounter, kSplitClaim);
+      if (tid == 0) sBcast[0] = ticket;
       __syncthreads();
       const uint32_t first = sBcast[0];
-      if (first >= p.totalTiles) break;
-      const uint32_t last = min(first + kSplitClaim, p.totalTiles);
-      uint32_t tile = first;
-      while (tile < last) {
+      __syncthreads();
+      if (first >= totalSlices) break;
+      if (tid == 0) ticket = atomicAdd(p.splitCounter, p.splitClaim);
+      const uint32_t last = min(first + p.splitClaim, totalSlices);
+      for (uint32_t sl = first; sl < last; ++sl) {
+        const uint32_t tile = sl >> sliceShift;
         const uint32_t e = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tile, guess);
         guess = e;
+        if (e != accElem) {
+          if (accSlices) publish();
+          accElem = e;
+        }
         const Elem el = p.sp.elems[e];
-        const uint32_t n = el.n;
-        const uint32_t elemEnd = p.sp.elems[e + 1].tileBase;
-        const uint32_t stop = min(last, elemEnd);
-        const uint32_t count = stop - tile;
-        for (; tile < stop; ++tile) {
-          if constexpr (FT == kFtNone)
-            histTileBytes<kFusedThreads>((const uint8_t*)el.in, n, (tile - el.tileBase) * kTileSyms, sh);
-          else
-            splitTile<FT, kFusedThreads>(p.sp, e, el, n, tile, sh);
+        if constexpr (FT == kFtNone) {
+          const uint32_t off = (tile - el.tileBase) * kTileSyms + (sl & ((1u << sliceShift) - 1u)) * sliceWords;
+          histTileBytes<kFusedThreads>((const uint8_t*)el.in, el.n, off, sliceWords, sh);
+        } else {
+          splitTile<FT, kFusedThreads>(p.sp, e, el, el.n, tile, sh, sliceWords, sl & ((1u << sliceShift) - 1u));
         }
-        __syncthreads();
-        splitHistFlush<kFusedThreads>(sh, p.sp.hist0 + (size_t)e * 256, tid);
-        __threadfence(); // plane, raw bytes and histogram of these tiles before the tile count
-        __syncthreads();
-        if (tid == 0) {
-          const uint32_t done = atomicAdd(&p.tilesDone[e], count) + count;
-          sBcast[1] = done == elemEnd - el.tileBase ? 1u : 0u;
-        }
-        __syncthreads();
-        if (sBcast[1]) { // this CTA completed the element: its histogram is final
-          __threadfence();
-          normalizeElement<kFusedThreads>(p.sp.hist0 + (size_t)e * 256, n, PB, p.ep.table + (size_t)e * 256, normSm);
-          __threadfence();
-          __syncthreads();
-          if (tid == 0) stRelease(p.ready + e, 1u);
-        }
-        __syncthreads(); // sBcast is rewritten after this point
+        ++accSlices;
       }
     }
+    if (accSlices) publish();
     __syncthreads();
   }
 
@@ -228,6 +249,27 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   if (splitPerSm >= (uint32_t)perSm) splitPerSm = (uint32_t)perSm - 1;
   // (few elements: making every CTA split first was measured slower - fp32 1 x 1 GiB 0.81 ms vs 0.72 ms)
   p.splitCtasPerSm = splitPerSm;
+  // Granularity of the split claims. Many elements: two whole tiles per claim, so that a CTA's counts are flushed
+  // once per 65536 words. Elements so large that every split CTA gets at least a tile's worth of each anyway:
+  // 4096-word slices in order, so that the CTAs sweep one contiguous front through memory.
+  p.sliceShift = 0;
+  p.splitClaim = 2;
+  {
+    const uint64_t splitCtas = (uint64_t)splitPerSm * (uint64_t)smCount();
+    if ((uint64_t)p.totalTiles >= splitCtas * (uint64_t)p.sp.numElems) {
+      p.sliceShift = 3;
+      p.splitClaim = 1;
+      // nothing can be encoded before the first table exists and there are few tables to wait for: all CTAs
+      // but one per SM split (fp32 1 x 1 GiB on B200: 0.73 ms with 3 split CTAs per SM and whole tiles,
+      // 0.69 ms with 9 and slices; 9 with whole tiles thrash DRAM: 0.81 ms)
+      if (!getenv("DGB_FUSED_SPLIT_CTAS")) p.splitCtasPerSm = (uint32_t)perSm - 1;
+    }
+    if (const char* e = getenv("DGB_SPLIT_SLICE_SHIFT")) { // experiment knob
+      p.sliceShift = (uint32_t)atoi(e);
+      p.splitClaim = p.sliceShift ? 1 : 2;
+    }
+    if (const char* e = getenv("DGB_SPLIT_CLAIM")) p.splitClaim = (uint32_t)max(1, atoi(e));
+  }
   // enough CTAs for the work, never more than fit at once (encode warps wait on split CTAs)
   p.ep.runShift = chooseRunShift(p.totalTiles, (uint32_t)smCount() * kEncCtasPerSm * kEncWarps);
   const uint32_t want = divUp(p.totalTiles << p.ep.runShift, kEncWarps) + p.totalTiles;
