@@ -59,6 +59,10 @@ def _load():
     L.dgb_ans_encode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp]
     L.dgb_ans_decode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp, vp]
     L.dgb_host_release.restype = None
+    L.dgb_peer_alloc.argtypes = [sz, vp, vp]
+    L.dgb_peer_open.argtypes = [vp, vp]
+    L.dgb_peer_close.argtypes = [vp]
+    L.dgb_peer_free.argtypes = [vp]
     L.dgb_profile_launches.restype = C.c_ulonglong
     L.dgb_profile_enable.argtypes = [i]
     L.dgb_set_fused_min_tiles.argtypes = [C.c_longlong]
@@ -71,7 +75,8 @@ def _load():
                  "dgb_ans_get_compressed_info", "dgb_float_compress", "dgb_float_compress_split_size",
                  "dgb_float_compress_sparse", "dgb_float_decompress", "dgb_float_decompress_split_size",
                  "dgb_float_decompress_sparse", "dgb_float_get_compressed_info", "dgb_float_compress_host",
-                 "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host"):
+                 "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host", "dgb_peer_alloc",
+                 "dgb_peer_open", "dgb_peer_close", "dgb_peer_free"):
         getattr(L, name).restype = i
     return L
 
@@ -89,7 +94,7 @@ EXPORTS = [
     "dgb_float_compress_split_size", "dgb_float_compress_sparse", "dgb_float_decompress",
     "dgb_float_decompress_split_size", "dgb_float_decompress_sparse", "dgb_float_get_compressed_info",
     "dgb_float_compress_host", "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host",
-    "dgb_host_release",
+    "dgb_host_release", "dgb_peer_alloc", "dgb_peer_open", "dgb_peer_close", "dgb_peer_free",
 ]
 
 

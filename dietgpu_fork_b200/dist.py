@@ -144,3 +144,146 @@ def all_to_all_compressed(t, out=None, group=None, codec=None):
 
 def _global_rank(group, group_rank):
     return group_rank if group is None else dist.get_global_rank(group, group_rank)
+
+
+# ---- peer-memory collectives: the exchange fused into the decompress kernel --------------------------------
+# Inside one NVLink / NVSwitch node the compressed bytes need not be moved by a collective at all: every rank
+# compresses into a buffer its peers can map (CUDA IPC), a stream-ordered barrier says "archives are complete",
+# and every rank's decompress kernel reads the peers' archives in place - its asynchronous copies pull exactly the
+# bytes it decodes over NVLink, tile by tile, while it decodes. No staging buffer, no size exchange (the archives
+# are self-describing), no host synchronisation anywhere in the call.
+class _Raw:
+    """pointer-only stand-in for a tensor (the codec layer only asks for data_ptr())"""
+
+    def __init__(self, ptr):
+        self._p = ptr
+
+    def data_ptr(self):
+        return self._p
+
+
+class PeerBuffers:
+    """One archive buffer per rank, mapped by every rank of the group (all on one node). Two halves are used in
+    turn by successive collectives, which is what lets one barrier per call suffice: a rank reaches the barrier
+    of call k + 1 only after its own decode of call k, so when any rank passes that barrier and later overwrites
+    half (k + 2) % 2 == k % 2, nobody is still reading it."""
+
+    def __init__(self, half_bytes, group=None, device=None):
+        import ctypes as C
+
+        from . import _capi
+        self._capi, self._C = _capi, C
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.half_bytes = (int(half_bytes) + 255) // 256 * 256
+        ptr, handle = C.c_void_p(), (C.c_uint8 * 64)()
+        _capi.check(_capi.lib.dgb_peer_alloc(2 * self.half_bytes, C.byref(ptr), handle), "dgb_peer_alloc")
+        self.local = ptr.value
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=self.device)
+        handles = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(handles, mine, group=group)
+        handles = handles.cpu().view(self.world, 64)
+        self.ptrs, self._opened = [], []
+        for r in range(self.world):
+            if r == self.rank:
+                self.ptrs.append(self.local)
+                continue
+            p = C.c_void_p()
+            h = (C.c_uint8 * 64)(*handles[r].tolist())
+            _capi.check(_capi.lib.dgb_peer_open(h, C.byref(p)), "dgb_peer_open")
+            self.ptrs.append(p.value)
+            self._opened.append(p.value)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._sizes = None
+        self.calls = 0
+        dist.barrier(group=group)
+
+    def barrier(self):
+        """Stream-ordered barrier: a one-word all-reduce. It completes on a rank's stream only after every rank's
+        stream has reached it; the host does not wait."""
+        dist.all_reduce(self._flag, group=self.group)
+
+    def next_half(self):
+        off = (self.calls & 1) * self.half_bytes
+        self.calls += 1
+        return off
+
+    def sizes_scratch(self, n):
+        if self._sizes is None or self._sizes.numel() < n:
+            self._sizes = torch.zeros(n, dtype=torch.int32, device=self.device)
+        return self._sizes
+
+    def close(self):
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        for p in self._opened:
+            self._capi.lib.dgb_peer_close(self._C.c_void_p(p))
+        self._opened = []
+        if self.local:
+            self._capi.lib.dgb_peer_free(self._C.c_void_p(self.local))
+            self.local = 0
+
+
+def peer_bytes_needed(dtype, numel, num_chunks=1):
+    """Bytes of one PeerBuffers half for collectives over tensors of `numel` elements cut into `num_chunks`."""
+    from . import codec
+    per = _round_up(-(-numel // max(1, num_chunks)), 8)
+    return max(1, num_chunks) * _round_up(codec.get_max_float_compressed_size(codec.FLOAT_TYPE_OF_DTYPE[dtype], per), 256)
+
+
+def all_gather_compressed_peer(t, peers, out=None, num_chunks=1, temp=None, prob_bits=10):
+    """All-gather of equal-sized float shards in which the exchange IS the decompress: every rank compresses its
+    shard into its peer-visible buffer, and decodes every rank's archives from where they lie. Returns `out` of
+    shape [world, *t.shape], bit-identical to the uncompressed all-gather."""
+    from . import codec
+    ft = codec.FLOAT_TYPE_OF_DTYPE[t.dtype]
+    world = peers.world
+    flat = t.contiguous().view(-1)
+    chunks = _chunks(flat, num_chunks)
+    stride = _round_up(codec.get_max_float_compressed_size(ft, chunks[0].numel()), 256)
+    assert stride * len(chunks) <= peers.half_bytes, "PeerBuffers too small (see peer_bytes_needed)"
+    if out is None:
+        out = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+    out_flat = out.view(world, -1)
+    half = peers.next_half()
+    rows = [_Raw(peers.local + half + c * stride) for c in range(len(chunks))]
+    codec.float_compress(ft, chunks, rows, peers.sizes_scratch(len(chunks)), prob_bits, False, temp=temp)
+    peers.barrier()
+    # Decode order = read order (the kernel takes tiles in list order): rank i starts with rank i + 1's archives,
+    # then i + 2's, ... and its own last, so that at any moment every source is read by one peer only instead
+    # of all ranks pulling from the same GPU.
+    ins, outs = [], []
+    for k in range(1, world + 1):
+        r = (peers.rank + k) % world
+        off = 0
+        for c, ch in enumerate(chunks):
+            ins.append(_Raw(peers.ptrs[r] + half + c * stride))
+            outs.append(out_flat[r].narrow(0, off, ch.numel()))
+            off += ch.numel()
+    codec.float_decompress(ft, ins, outs, None, None, prob_bits, False, temp=temp)
+    return out
+
+
+def all_to_all_compressed_peer(t, peers, out=None, temp=None, prob_bits=10):
+    """All-to-all of float chunks (t[j] goes to rank j) through peer memory: one batched compress of the outgoing
+    chunks into the own buffer, a barrier, one batched decompress that reads row `rank` of every peer's buffer."""
+    from . import codec
+    ft = codec.FLOAT_TYPE_OF_DTYPE[t.dtype]
+    world, rank = peers.world, peers.rank
+    assert t.size(0) == world, "first dimension must be the group size"
+    t = t.contiguous()
+    if out is None:
+        out = torch.empty_like(t)
+    send = [t[j].view(-1) for j in range(world)]
+    stride = _round_up(codec.get_max_float_compressed_size(ft, send[0].numel()), 256)
+    assert stride * world <= peers.half_bytes, "PeerBuffers too small (see peer_bytes_needed)"
+    half = peers.next_half()
+    rows = [_Raw(peers.local + half + j * stride) for j in range(world)]
+    codec.float_compress(ft, send, rows, peers.sizes_scratch(world), prob_bits, False, temp=temp)
+    peers.barrier()
+    order = [(rank + k) % world for k in range(1, world + 1)]  # staggered sources, own chunk last (see above)
+    ins = [_Raw(peers.ptrs[i] + half + rank * stride) for i in order]
+    outs = [out[i].view(-1) for i in order]
+    codec.float_decompress(ft, ins, outs, None, None, prob_bits, False, temp=temp)
+    return out

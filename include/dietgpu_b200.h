@@ -176,6 +176,20 @@ int dgb_ans_decode_host(int prob_bits, int use_checksum, uint32_t num_in_batch, 
 /* Frees the cached staging buffers and streams of the host-buffer calls (all devices). */
 void dgb_host_release(void);
 
+/* ---- peer buffers (compressed collectives inside one NVLink / NVSwitch node) ------------------- */
+/* A device buffer that the other ranks (processes) of the node can map: cudaMalloc + CUDA IPC. A rank
+ * compresses into its own buffer; after a stream-ordered barrier every rank passes the PEER pointers as `in`
+ * of dgb_float_decompress / dgb_ans_decode_batch_pointer, and the decoder pulls exactly the compressed bytes
+ * over NVLink while it decodes (dietgpu_fork_b200/dist.py: all_gather_compressed_peer,
+ * all_to_all_compressed_peer). No reference counterpart (the reference is single-GPU). */
+#define DGB_PEER_HANDLE_BYTES 64
+/* allocates `bytes` on the current device; writes the device pointer and its 64-byte IPC handle */
+int dgb_peer_alloc(size_t bytes, void** dev_ptr, void* handle64);
+/* maps another process's buffer (peer access is enabled on first use); *peer_ptr is valid on this device */
+int dgb_peer_open(const void* handle64, void** peer_ptr);
+int dgb_peer_close(void* peer_ptr);
+int dgb_peer_free(void* dev_ptr);
+
 /* Scratch bytes the last finished call on this thread took (from temp_dev plus the pool): what the
  * reference reports through StackDeviceMemory::getMaxMemoryUsage(),
  * dietgpu/utils/StackDeviceMemory.h:196-200. */

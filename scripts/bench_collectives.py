@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--chunks", type=int, default=4)
+    ap.add_argument("--peer", type=int, default=1, help="also time the peer-memory collectives (CUDA IPC)")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -64,6 +65,23 @@ def main():
     if rank == 0:
         print(json.dumps(res), flush=True)
 
+    # --- all-gather through peer memory (exchange fused into the decompress kernel) ---
+    peers = None
+    if a.peer:
+        peers = dgd.PeerBuffers(max(dgd.peer_bytes_needed(torch.bfloat16, n, a.chunks),
+                                    dgd.peer_bytes_needed(torch.bfloat16, n // world, 1) * world))
+        out.zero_()
+        dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=a.chunks, temp=temp)
+        torch.cuda.synchronize()
+        assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather is not bit exact"
+        t_peer = timed(lambda: dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=a.chunks, temp=temp),
+                       a.steps, a.warmup)
+        assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather is not bit exact (timed)"
+        if rank == 0:
+            print(json.dumps({"collective": "all_gather_peer", "n_gpus": world, "shard_mib": a.mib, "chunks": a.chunks,
+                              "nccl_raw_ms": t_raw, "peer_ms": t_peer, "nccl_raw_gbs": delivered / t_raw / 1e6,
+                              "peer_effective_gbs": delivered / t_peer / 1e6}), flush=True)
+
     # --- all-to-all: mib/world MiB to every peer ---
     per = n // world
     send = shard[:per * world].view(world, per)
@@ -80,6 +98,18 @@ def main():
            "nccl_raw_gbs": delivered / t_raw / 1e6, "compressed_effective_gbs": delivered / t_cmp / 1e6}
     if rank == 0:
         print(json.dumps(res), flush=True)
+    if peers is not None:
+        out2.zero_()
+        dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp)
+        torch.cuda.synchronize()
+        assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "peer all-to-all is not bit exact"
+        t_peer = timed(lambda: dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp), a.steps, a.warmup)
+        assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "peer all-to-all is not bit exact (timed)"
+        if rank == 0:
+            print(json.dumps({"collective": "all_to_all_peer", "n_gpus": world, "chunk_mib": per * 2 / (1 << 20),
+                              "nccl_raw_ms": t_raw, "peer_ms": t_peer, "nccl_raw_gbs": delivered / t_raw / 1e6,
+                              "peer_effective_gbs": delivered / t_peer / 1e6}), flush=True)
+        peers.close()
     dist.destroy_process_group()
 
 
