@@ -46,7 +46,9 @@ struct FusedParams {
   uint32_t totalTiles;
   uint32_t splitCtasPerSm;
   uint32_t sliceShift; // log2(slices per tile) the split role claims work in
-  uint32_t splitClaim; // slices per claim
+  uint32_t splitClaim; // slices per claim beyond the fine prefix
+  uint32_t fineSlices; // the first fineSlices slices are claimed one at a time (multiple of splitClaim)
+  uint32_t* splitCounterB; // zeroed: claims beyond the fine prefix
   unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run end, end, smid/role, encode end}
 };
 
@@ -148,18 +150,31 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
       __syncthreads(); // sBcast is rewritten after this point
       accSlices = 0;
     };
-    // the next claim is requested before the current one is processed (thread 0 holds the ticket in a register)
+    // Claims: single slices over the fine prefix (the first elements complete early and in quick succession, so
+    // the encode warps do not wait for a whole round of coarse claims), splitClaim slices at a time after it.
+    // The next claim is requested before the current one is processed (thread 0 holds the ticket in a register).
+    const uint32_t fineSlices = p.fineSlices, perTile = 1u << sliceShift;
+    bool fine = fineSlices != 0;
+    auto claim = [&]() -> uint32_t { // thread 0 only
+      if (fine) {
+        const uint32_t t = atomicAdd(p.splitCounter, 1u);
+        if (t < fineSlices) return t;
+        fine = false;
+      }
+      return fineSlices + atomicAdd(p.splitCounterB, p.splitClaim);
+    };
     uint32_t ticket = 0;
-    if (tid == 0) ticket = atomicAdd(p.splitCounter, p.splitClaim);
+    if (tid == 0) ticket = claim();
     for (;;) {
       if (tid == 0) sBcast[0] = ticket;
       __syncthreads();
       const uint32_t first = sBcast[0];
       __syncthreads();
       if (first >= totalSlices) break;
-      if (tid == 0) ticket = atomicAdd(p.splitCounter, p.splitClaim);
-      const uint32_t last = min(first + p.splitClaim, totalSlices);
-      for (uint32_t sl = first; sl < last; ++sl) {
+      if (tid == 0) ticket = claim();
+      const uint32_t last = min(first + (first < fineSlices ? 1u : p.splitClaim), totalSlices);
+      uint32_t sl = first;
+      while (sl < last) {
         const uint32_t tile = sl >> sliceShift;
         const uint32_t e = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tile, guess);
         guess = e;
@@ -168,13 +183,18 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
           accElem = e;
         }
         const Elem el = p.sp.elems[e];
+        const uint32_t sub = sl & (perTile - 1u);
+        const bool whole = sub == 0 && sl + perTile <= last; // a whole tile of this claim in one go
+        const uint32_t words = whole ? kTileSyms : sliceWords;
         if constexpr (FT == kFtNone) {
-          const uint32_t off = (tile - el.tileBase) * kTileSyms + (sl & ((1u << sliceShift) - 1u)) * sliceWords;
-          histTileBytes<kFusedThreads>((const uint8_t*)el.in, el.n, off, sliceWords, sh);
+          const uint32_t off = (tile - el.tileBase) * kTileSyms + sub * sliceWords;
+          histTileBytes<kFusedThreads>((const uint8_t*)el.in, el.n, off, words, sh);
         } else {
-          splitTile<FT, kFusedThreads>(p.sp, e, el, el.n, tile, sh, sliceWords, sl & ((1u << sliceShift) - 1u));
+          splitTile<FT, kFusedThreads>(p.sp, e, el, el.n, tile, sh, words, whole ? 0u : sub);
         }
-        ++accSlices;
+        const uint32_t step = whole ? perTile : 1u;
+        accSlices += step;
+        sl += step;
       }
     }
     if (accSlices) publish();
@@ -252,23 +272,22 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   // Granularity of the split claims. Many elements: two whole tiles per claim, so that a CTA's counts are flushed
   // once per 65536 words. Elements so large that every split CTA gets at least a tile's worth of each anyway:
   // 4096-word slices in order, so that the CTAs sweep one contiguous front through memory.
-  p.sliceShift = 0;
-  p.splitClaim = 2;
+  p.sliceShift = 3;
+  p.splitClaim = 16;
+  p.fineSlices = 0;
   {
     const uint64_t splitCtas = (uint64_t)splitPerSm * (uint64_t)smCount();
+    if (const char* e = getenv("DGB_SPLIT_FINE_TILES")) p.fineSlices = (uint32_t)atoi(e) << p.sliceShift; // experiment knob
     if ((uint64_t)p.totalTiles >= splitCtas * (uint64_t)p.sp.numElems) {
-      p.sliceShift = 3;
-      p.splitClaim = 1;
+      p.fineSlices = 0xfffffff0u; // everything
+      p.splitClaim = 16;
       // nothing can be encoded before the first table exists and there are few tables to wait for: all CTAs
       // but one per SM split (fp32 1 x 1 GiB on B200: 0.73 ms with 3 split CTAs per SM and whole tiles,
       // 0.69 ms with 9 and slices; 9 with whole tiles thrash DRAM: 0.81 ms)
       if (!getenv("DGB_FUSED_SPLIT_CTAS")) p.splitCtasPerSm = (uint32_t)perSm - 1;
     }
-    if (const char* e = getenv("DGB_SPLIT_SLICE_SHIFT")) { // experiment knob
-      p.sliceShift = (uint32_t)atoi(e);
-      p.splitClaim = p.sliceShift ? 1 : 2;
-    }
-    if (const char* e = getenv("DGB_SPLIT_CLAIM")) p.splitClaim = (uint32_t)max(1, atoi(e));
+    if (p.fineSlices > (p.totalTiles << p.sliceShift)) p.fineSlices = p.totalTiles << p.sliceShift;
+    p.fineSlices = p.fineSlices / p.splitClaim * p.splitClaim;
   }
   // enough CTAs for the work, never more than fit at once (encode warps wait on split CTAs)
   p.ep.runShift = chooseRunShift(p.totalTiles, (uint32_t)smCount() * kEncCtasPerSm * kEncWarps);
@@ -328,13 +347,14 @@ int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, ui
   p.sp.checksum = checksum;
   p.sp.useChecksum = useChecksum;
   p.splitCounter = es.fusedCtrl;
+  p.splitCounterB = es.fusedCtrl + kFusedCtrlSplitB;
   p.smTicket = es.fusedCtrl + 1;
   p.tilesDone = es.fusedCtrl + kFusedCtrlFixed;
   p.ready = p.tilesDone + a.numElems;
   p.runsDone = p.ready + a.numElems;
   p.ep.tileWords = p.runsDone + a.numElems;
   static const bool separateCoalesce = getenv("DGB_FUSED_COALESCE") && atoi(getenv("DGB_FUSED_COALESCE")) == 0;
-  p.coalClaim = separateCoalesce ? nullptr : es.fusedCtrl + kFusedCtrlFixed - 1; // experiment knob
+  p.coalClaim = separateCoalesce ? nullptr : es.fusedCtrl + kFusedCtrlCoal; // experiment knob
   p.ep.ready = p.ready;
   p.totalTiles = totalTiles;
   int rc;

@@ -131,7 +131,10 @@ struct EncodeArgs {
 };
 // Enqueues normalise + encode for one exponent plane / byte stream. Scratch comes from `tmp`.
 // A slice of the work list: elements [e0, e1) with their 8-block tiles and 4096-symbol blocks.
-constexpr uint32_t kFusedCtrlFixed = 1 + 512 + 1; // split tile counter + per-SM role tickets + compaction claim counter
+// fused kernel control words: [0] split counter (fine prefix) | [1, 513) per-SM role tickets | [513] compaction
+// claim counter | [514] split counter (coarse claims after the prefix) | [515] unused
+constexpr uint32_t kFusedCtrlFixed = 516;
+constexpr uint32_t kFusedCtrlCoal = 513, kFusedCtrlSplitB = 514;
 
 struct WorkRange {
   uint32_t e0, e1, tile0, tile1, blk0, blk1;
