@@ -187,8 +187,8 @@ __device__ __forceinline__ uint32_t decStep(uint32_t& state, uint32_t lutAddr, u
       "lop3.b32 a, a, %6, %3, 0xEA;\n"        // ((state << 2) & mask) | lutAddr
       "ld.shared.u32 %2, [a];\n"
       "shr.u32 hi, %0, %7;\n"
-      "shr.u32 t, %2, 8;\n"
-      "and.b32 t, t, 0xfff;\n"                // pdf
+      "mul.lo.u32 t, %2, 4096;\n"             // pdf = (e << 12) >> 20: the shift left runs on the FMA pipe
+      "shr.u32 t, t, 20;\n"                   //   (IMAD.SHL), one ALU instruction less than shr + and
       "shr.u32 b, %2, 20;\n"                  // slot - cdf
       "mad.lo.u32 ns, t, hi, b;\n"
       "setp.lt.u32 p, ns, 32768;\n"
@@ -198,7 +198,7 @@ __device__ __forceinline__ uint32_t decStep(uint32_t& state, uint32_t lutAddr, u
       "mad.lo.u32 ra, pre, 0xfffffffe, %1;\n" // ptr - 2 * (readers at or above this lane)
       "lop3.b32 ra, ra, %8, %4, 0xEA;\n"      // (ra & ringMask) | ringAddr
       "ld.shared.u16 w, [ra];\n"              // every lane loads (a valid ring slot); only readers use it
-      "@p prmt.b32 ns, w, ns, 0x5410;\n"      // (ns << 16) | w
+      "@p mad.lo.u32 ns, ns, 65536, w;\n"     // (ns << 16) | w on the FMA pipe (w < 65536, ns < 32768)
       "popc.b32 c, v;\n"
       "mad.lo.u32 %1, c, 0xfffffffe, %1;\n"
       "mov.b32 %0, ns;\n"
