@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) k_coalesce(const EncParams p, int probBit
   const uint32_t grp = firstBlk / kGroupBlocks;
   const uint32_t* groupSum = p.groupWords + el.groupBase;
   uint32_t part = 0;
-  for (uint32_t g = tid; g < grp; g += 256) part += groupSum[g];
+  for (uint32_t g = tid; g < grp; g += 256) part += groupSum[g] & kGroupSizeMask; // (count bits: fused kernel only)
   for (uint32_t b = grp * kGroupBlocks + tid; b < firstBlk; b += 256)
     part += roundUp(p.blockWords[el.blockBase + b], 8);
   part = warpSum(part);

@@ -167,6 +167,10 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
 constexpr uint32_t kEncWarps = 4;
 constexpr uint32_t kEncCtasPerSm = 10;
 constexpr uint32_t kGroupBlocks = 256;           // compaction: blocks per size group
+// fused kernel: the per-group / per-tile size sums carry a count of finished blocks above the size bits
+// (a group holds < 2^20 words, a tile < 2^24)
+constexpr uint32_t kGroupCountShift = 20, kGroupCountOne = 1u << kGroupCountShift, kGroupSizeMask = kGroupCountOne - 1u;
+constexpr uint32_t kTileCountShift = 24, kTileCountOne = 1u << kTileCountShift, kTileSizeMask = kTileCountOne - 1u;
 constexpr uint32_t kEncChunkRows = 16;            // rows per staged symbol chunk (512 symbols, one 16-byte load per lane)
 constexpr uint32_t kEncChunk = kEncChunkRows * 32;
 // Run = consecutive blocks one warp encodes as one stream: 2 when there is enough work to fill the GPU with such
@@ -385,16 +389,14 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     const uint32_t gb = w.blockBase + blk;
     uint4* slot = (uint4*)(p.scratch + (size_t)gb * kSlotBytes);
     uint32_t bytes = outPtr - stageAddr;
+    uint32_t words = 0, paddedWords = 0;
     __syncwarp();
     if (final) {
       const uint32_t padded = roundUp(bytes, 16);
       if (bytes + 2 * lane < padded) *(uint16_t*)(stage + bytes + 2 * lane) = 0;
       __syncwarp();
-      if (lane == 0) {
-        p.blockWords[gb] = flushedVecs * 8 + (bytes >> 1);
-        atomicAdd(&w.groupSum[blk / kGroupBlocks], flushedVecs * 8 + (padded >> 1));
-        if (FUSED) atomicAdd(p.tileWords + w.tileBase + blk / kTileBlocks, flushedVecs * 8 + (padded >> 1));
-      }
+      words = flushedVecs * 8 + (bytes >> 1);
+      paddedWords = flushedVecs * 8 + (padded >> 1);
       bytes = padded;
     }
     const uint32_t nv = bytes >> 4;
@@ -402,7 +404,18 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     if (final) {
       // final lane states go straight to their place in the archive (:584-589)
       ((uint32_t*)(w.ans + kAnsFixedBytes))[blk * 32 + lane] = state;
-      __syncwarp(); // the staging buffer is reused by the next block
+      __syncwarp(); // the staging buffer is reused by the next block; the slot is complete
+      if (lane == 0) {
+        p.blockWords[gb] = words;
+        if (FUSED) {
+          // sizes and, in the high bits, the number of finished blocks (release: slot and size first); the
+          // in-kernel compaction of a tile starts as soon as these counts say its predecessors are encoded
+          redRelease(&w.groupSum[blk / kGroupBlocks], paddedWords + kGroupCountOne);
+          redRelease(p.tileWords + w.tileBase + blk / kTileBlocks, paddedWords + kTileCountOne);
+        } else {
+          atomicAdd(&w.groupSum[blk / kGroupBlocks], paddedWords);
+        }
+      }
       state = kStateMin;
       outPtr = stageAddr;
       flushedVecs = 0;
@@ -483,8 +496,38 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
 // Deliberately not inlined: it runs once per 8 blocks and must not take registers from the row loop (the caller
 // passes its __grid_constant__ parameter block).
 // ---------------------------------------------------------------------------------------------
+// Fused kernel: blocks until every block of tiles [0, t] of element e is encoded (t = tk - tileBase), i.e. until the
+// sizes coalesceTileWarp sums up are final and the tile's own slots are complete. Whole groups before the tile's
+// group are checked through the group counters, the tiles of its own group one per lane. Runs are handed out in
+// order, so in steady state the first look succeeds.
+// `wait` false: one look, returns whether the tile is ready (used between runs, where a warp must not block).
+static __device__ __noinline__ bool waitTilesEncoded(const EncParams& p, uint32_t e, uint32_t tk, uint32_t lane,
+                                                     bool wait) {
+  const Elem el = p.a.elems[e];
+  const uint32_t t = tk - el.tileBase;
+  const uint32_t nb = divUp(el.n, kBlockSyms);
+  if (t * kTileBlocks >= nb) return true; // no blocks in this tile (empty element or padding tile)
+  constexpr uint32_t kGroupTiles = kGroupBlocks / kTileBlocks;
+  const uint32_t grp = t / kGroupTiles;
+  const uint32_t* groupSum = p.groupWords + el.groupBase;
+  const uint32_t* tiles = p.tileWords + el.tileBase;
+  uint32_t ns = 100;
+  for (;;) {
+    bool ok = true;
+    for (uint32_t g = lane; g < grp; g += 32) ok = ok && (ldRelaxed(groupSum + g) >> kGroupCountShift) == kGroupBlocks;
+    const uint32_t j = grp * kGroupTiles + lane;
+    if (j <= t) ok = ok && (ldRelaxed(tiles + j) >> kTileCountShift) == min(kTileBlocks, nb - j * kTileBlocks);
+    if (__all_sync(0xffffffffu, ok)) break;
+    if (!wait) return false;
+    __nanosleep(ns);
+    if (ns < 1600) ns *= 2;
+  }
+  asm volatile("fence.acq_rel.gpu;" ::: "memory");
+  return true;
+}
+
 static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int probBits, uint32_t e, uint32_t tk,
-                                                     uint32_t lane, uint8_t* stage) {
+                                                     uint32_t lane, uint8_t* stage, uint32_t stageBytes) {
   const EncodeArgs& a = p.a;
   const Elem el = a.elems[e];
   const uint32_t t = tk - el.tileBase;
@@ -512,12 +555,12 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
     blkLen = min(kBlockSyms, n - myBlk * kBlockSyms);
   }
   uint32_t part = 0;
-  if (grp * kGroupTiles + lane < t) part = __ldcg(p.tileWords + tk - t + grp * kGroupTiles + lane);
+  if (grp * kGroupTiles + lane < t) part = __ldcg(p.tileWords + tk - t + grp * kGroupTiles + lane) & kTileSizeMask;
   for (uint32_t g = lane; g < grp; g += 128) { // 4 loads in flight per lane (a 4 GiB element has 4096 groups)
-    const uint32_t x0 = __ldcg(groupSum + g);
-    const uint32_t x1 = g + 32 < grp ? __ldcg(groupSum + g + 32) : 0u;
-    const uint32_t x2 = g + 64 < grp ? __ldcg(groupSum + g + 64) : 0u;
-    const uint32_t x3 = g + 96 < grp ? __ldcg(groupSum + g + 96) : 0u;
+    const uint32_t x0 = __ldcg(groupSum + g) & kGroupSizeMask;
+    const uint32_t x1 = g + 32 < grp ? __ldcg(groupSum + g + 32) & kGroupSizeMask : 0u;
+    const uint32_t x2 = g + 64 < grp ? __ldcg(groupSum + g + 64) & kGroupSizeMask : 0u;
+    const uint32_t x3 = g + 96 < grp ? __ldcg(groupSum + g + 96) & kGroupSizeMask : 0u;
     part += x0 + x1 + x2 + x3;
   }
   const uint32_t excl = warpSum(part);
@@ -533,7 +576,7 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
   if (blkLen) ((uint2*)(ans + kAnsFixedBytes + 128u * nb))[myBlk] = make_uint2((blkLen << 16) | words, startWord);
 
   // ---- payload ----
-  constexpr uint32_t kCap = kEncWarpSmem / 16; // staging capacity in 16-byte vectors
+  const uint32_t kCap = stageBytes / 16; // staging capacity in 16-byte vectors
   const uint32_t stageAddr = smemAddr(stage);
   uint4* dst = (uint4*)(ans + ansOverhead(nb) + 2 * (size_t)excl); // the tile's first vector in the archive
   const uint8_t* slots = p.scratch + (size_t)(el.blockBase + firstBlk) * kSlotBytes;

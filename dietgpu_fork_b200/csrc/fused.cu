@@ -17,10 +17,11 @@
 //   * encode warps claim runs of 4 blocks in the same order, wait (acquire) for the run's element, and encode
 //     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
 //   * a split CTA that finds no tile left becomes an encode CTA;
-//   * compaction (what k_coalesce does for the stand-alone encoder) is the warps' last job: every finished run
-//     bumps its element's run count (release); a warp that finds no run left takes tickets for 8-block compaction
-//     tiles, waits until the tile's element is completely encoded and copies the tile's blocks from their
-//     L2-resident scratch slots to their final place (every run is by then owned by a running warp).
+//   * compaction (what k_coalesce does for the stand-alone encoder) is the warps' last job: every finished block
+//     adds its size and a count of one to its tile's and its group's sum (release); a warp that finds no run left
+//     takes tickets for 8-block compaction tiles in order, waits until the tile and all tiles before it in the
+//     element are encoded (their sums are then final) and copies the tile's blocks from their L2-resident
+//     scratch slots to their final place (every run is by then owned by a running warp).
 // Split CTAs never wait and encode warps wait only for split CTAs, so every flag arrives; the grid is sized to be
 // co-resident.
 #include <cstdio>
@@ -49,6 +50,9 @@ struct FusedParams {
   uint32_t splitClaim; // slices per claim beyond the fine prefix
   uint32_t fineSlices; // the first fineSlices slices are claimed one at a time (multiple of splitClaim)
   uint32_t* splitCounterB; // zeroed: claims beyond the fine prefix
+  uint32_t tailSlices;     // the last tailSlices slices are claimed tailClaim at a time (short stragglers)
+  uint32_t tailClaim;
+  uint32_t compactBetweenRuns; // few huge elements: warps compact finished tiles between their runs
   unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run end, end, smid/role, encode end}
 };
 
@@ -98,11 +102,34 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
   }
 }
 
+// Between runs (batches of few huge elements only, where compaction would otherwise be a serial tail after the
+// last run): if the next compaction tile is already completely encoded, with everything before it in its element,
+// try to take exactly that ticket and compact it now, while its slots are hot in L2. A warp never blocks here (it
+// may hold the only claim on a run others wait for); the staging area is the warp's stage + ring, its encode
+// table stays intact. Not inlined: it must not take registers from the row loop.
+template <int PB>
+static __device__ __noinline__ void tryCompactOne(const FusedParams& p, uint32_t lane, uint8_t* stage) {
+  uint32_t tk = 0;
+  if (lane == 0) tk = ldRelaxed(p.coalClaim);
+  tk = __shfl_sync(0xffffffffu, tk, 0);
+  if (tk >= p.totalTiles) return;
+  uint32_t guess = 0;
+  const uint32_t ce = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tk, guess);
+  if (!waitTilesEncoded(p.ep, ce, tk, lane, false)) return;
+  uint32_t got = 0;
+  if (lane == 0) got = atomicCAS(p.coalClaim, tk, tk + 1u) == tk ? 1u : 0u;
+  got = __shfl_sync(0xffffffffu, got, 0);
+  if (!got) return;
+  __syncwarp();
+  coalesceTileWarp(p.ep, PB, ce, tk, lane, stage, kEncStageBytes + kEncRingBytes);
+  __syncwarp(); // stage and ring are free for the next run
+}
+
 template <int FT, int PB>
 __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(const __grid_constant__ FusedParams p) {
   if constexpr (FT != kFtNone) static_assert(FloatTraits<FT>::kPlanes == 1, "single exponent plane only");
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint32_t sBcast[2];
+  __shared__ uint32_t sBcast[3];
   const uint32_t tid = threadIdx.x;
   unsigned long long t0 = 0, t1 = 0, t2 = 0, tEnc = 0;
   uint32_t smidTrace = 0;
@@ -155,24 +182,34 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     // The next claim is requested before the current one is processed (thread 0 holds the ticket in a register).
     const uint32_t fineSlices = p.fineSlices, perTile = 1u << sliceShift;
     bool fine = fineSlices != 0;
+    // Towards the end the claims shrink (decided from a possibly stale look at the counter: any size is valid), so
+    // that no CTA is left with 65536 words to split while everybody else already encodes: encode warps take
+    // runs in order and would all queue up behind that one element.
+    uint32_t ticketLen = 1;
     auto claim = [&]() -> uint32_t { // thread 0 only
       if (fine) {
         const uint32_t t = atomicAdd(p.splitCounter, 1u);
+        ticketLen = 1;
         if (t < fineSlices) return t;
         fine = false;
       }
-      return fineSlices + atomicAdd(p.splitCounterB, p.splitClaim);
+      const uint32_t seen = fineSlices + ldRelaxed(p.splitCounterB);
+      ticketLen = seen + p.tailSlices >= totalSlices ? p.tailClaim : p.splitClaim;
+      return fineSlices + atomicAdd(p.splitCounterB, ticketLen);
     };
     uint32_t ticket = 0;
     if (tid == 0) ticket = claim();
     for (;;) {
-      if (tid == 0) sBcast[0] = ticket;
+      if (tid == 0) {
+        sBcast[0] = ticket;
+        sBcast[2] = ticketLen;
+      }
       __syncthreads();
       const uint32_t first = sBcast[0];
+      const uint32_t last = min(first + sBcast[2], totalSlices);
       __syncthreads();
       if (first >= totalSlices) break;
       if (tid == 0) ticket = claim();
-      const uint32_t last = min(first + (first < fineSlices ? 1u : p.splitClaim), totalSlices);
       uint32_t sl = first;
       while (sl < last) {
         const uint32_t tile = sl >> sliceShift;
@@ -214,10 +251,7 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     if (w.lane == 0) nextRun = atomicAdd(p.ep.runCounter, 1u);
     encodeRun<PB, true>(p.ep, w, run);
     if (p.trace && tid == 0 && t2 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); // end of first run
-    if (p.coalClaim) { // this run's slots, sizes and states, then its count (release)
-      __syncwarp();
-      if (w.lane == 0) redRelease(p.runsDone + w.curElem, 1u);
-    }
+    if (p.compactBetweenRuns) tryCompactOne<PB>(p, w.lane, w.stage);
     run = __shfl_sync(0xffffffffu, nextRun, 0);
   }
   if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tEnc));
@@ -233,17 +267,8 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
       if (tk >= p.totalTiles) break;
       const uint32_t ce = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tk, guess);
       guess = ce;
-      if (w.lane == 0) {
-        const uint32_t want = (p.sp.elems[ce + 1].tileBase - p.sp.elems[ce].tileBase) << p.ep.runShift;
-        uint32_t ns = 250; // growing back-off: thousands of warps may wait for the same element
-        while (ldRelaxed(p.runsDone + ce) != want) {
-          __nanosleep(ns);
-          if (ns < 2000) ns *= 2;
-        }
-        (void)ldAcquire(p.runsDone + ce);
-      }
-      __syncwarp();
-      coalesceTileWarp(p.ep, PB, ce, tk, w.lane, w.tabSmem);
+      (void)waitTilesEncoded(p.ep, ce, tk, w.lane, true); // the tile and everything before it in its element
+      coalesceTileWarp(p.ep, PB, ce, tk, w.lane, w.tabSmem, kEncWarpSmem);
     }
   }
   if (p.trace && tid == 0) {
@@ -275,17 +300,30 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   p.sliceShift = 3;
   p.splitClaim = 16;
   p.fineSlices = 0;
+  p.compactBetweenRuns = 0;
   {
     const uint64_t splitCtas = (uint64_t)splitPerSm * (uint64_t)smCount();
     if (const char* e = getenv("DGB_SPLIT_FINE_TILES")) p.fineSlices = (uint32_t)atoi(e) << p.sliceShift; // experiment knob
     if ((uint64_t)p.totalTiles >= splitCtas * (uint64_t)p.sp.numElems) {
       p.fineSlices = 0xfffffff0u; // everything
+      // and compaction is interleaved with the runs (fp32 1 x 1 GiB: 0.682 -> 0.669 ms; for batches of many
+      // elements, whose compaction overlaps the encoding of later elements anyway, it costs 3 %)
+      p.compactBetweenRuns = 1;
       p.splitClaim = 16;
       // nothing can be encoded before the first table exists and there are few tables to wait for: all CTAs
       // but one per SM split (fp32 1 x 1 GiB on B200: 0.73 ms with 3 split CTAs per SM and whole tiles,
       // 0.69 ms with 9 and slices; 9 with whole tiles thrash DRAM: 0.81 ms)
       if (!getenv("DGB_FUSED_SPLIT_CTAS")) p.splitCtasPerSm = (uint32_t)perSm - 1;
     }
+    {
+      uint32_t rounds = 2, tail = 8; // B200: single tiles over the last two rounds: fp32 64 x 16 MiB 0.557 -> 0.542 ms, bf16 equal; 2- and 4-slice claims are slower
+      if (const char* e = getenv("DGB_SPLIT_TAIL_ROUNDS")) rounds = (uint32_t)atoi(e); // experiment knobs
+      if (const char* e = getenv("DGB_SPLIT_TAIL_CLAIM")) tail = (uint32_t)max(1, atoi(e));
+      p.tailSlices = rounds * (uint32_t)splitCtas * p.splitClaim;
+      p.tailClaim = tail;
+    }
+    if (const char* e = getenv("DGB_COMPACT_BETWEEN_RUNS")) p.compactBetweenRuns = atoi(e) != 0; // experiment knob
+    if (!p.coalClaim) p.compactBetweenRuns = 0;
     if (p.fineSlices > (p.totalTiles << p.sliceShift)) p.fineSlices = p.totalTiles << p.sliceShift;
     p.fineSlices = p.fineSlices / p.splitClaim * p.splitClaim;
   }
