@@ -66,8 +66,10 @@ __device__ __forceinline__ void histFlush(uint32_t* sh, uint32_t* gHist, uint32_
 
 __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elems, uint32_t numElems,
                                                    uint32_t totalTiles, uint32_t tilesPerCta,
-                                                   uint32_t* __restrict__ hist) {
+                                                   uint32_t* __restrict__ hist, uint32_t* __restrict__ normTilesDone,
+                                                   uint2* __restrict__ normTable, int normProbBits) {
   __shared__ uint32_t sh[8 * 256 * kHistRep];
+  __shared__ uint32_t sLast;
   const uint32_t tid = threadIdx.x;
   for (uint32_t i = tid; i < 8 * 256 * kHistRep; i += 256) sh[i] = 0;
   __syncthreads();
@@ -77,10 +79,32 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
   uint32_t t0 = blockIdx.x * tilesPerCta;
   uint32_t t1 = min(t0 + tilesPerCta, totalTiles);
   uint32_t cur = 0xffffffffu;
+  // counts of element `cur` -> global bins; the CTA whose tiles complete the element also builds its encode table
+  // (saves the k_normalize launch: small batches are launch-latency bound)
+  auto finishElement = [&]() {
+    histFlush(sh, hist + cur * 256, tid);
+    if (normTilesDone) {
+      const uint32_t eb = elems[cur].tileBase, ee = elems[cur + 1].tileBase;
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) {
+        const uint32_t count = min(t1, ee) - max(t0, eb);
+        sLast = atomicAdd(&normTilesDone[cur], count) + count == ee - eb ? 1u : 0u;
+      }
+      __syncthreads();
+      if (sLast) {
+        __threadfence();
+        normalizeElement<256>(hist + (size_t)cur * 256, elems[cur].n, normProbBits, normTable + (size_t)cur * 256, sh);
+        __syncthreads();
+        for (uint32_t i = tid; i < 256 + 16; i += 256) sh[i] = 0; // bins used as scratch
+      }
+      __syncthreads();
+    }
+  };
   for (uint32_t tile = t0; tile < t1; ++tile) {
     uint32_t e = findElement(&elems[0].tileBase, sizeof(Elem) / 4, numElems, tile, cur);
     if (e != cur) {
-      if (cur != 0xffffffffu) histFlush(sh, hist + cur * 256, tid);
+      if (cur != 0xffffffffu) finishElement();
       cur = e;
     }
     const uint8_t* base = (const uint8_t*)elems[e].in;
@@ -112,18 +136,18 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
       histAddWord(wh, x0.x, rep); histAddWord(wh, x0.y, rep); histAddWord(wh, x0.z, rep); histAddWord(wh, x0.w, rep);
     }
   }
-  if (cur != 0xffffffffu) histFlush(sh, hist + cur * 256, tid);
+  if (cur != 0xffffffffu) finishElement();
 }
 
-int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist,
-                    cudaStream_t s) {
+int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s,
+                    uint32_t* normTilesDone, uint2* normTable, int normProbBits) {
   if (!totalTiles) return kOk;
   uint32_t ctas = min(totalTiles, (uint32_t)smCount() * 4u);
   uint32_t per = divUp(totalTiles, ctas);
   ctas = divUp(totalTiles, per);
   {
     ProfScope ps__("k_histBytes", s);
-    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist);
+    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist, normTilesDone, normTable, normProbBits);
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;
@@ -331,10 +355,11 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
   p.runShift = 2;
 }
 
-int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {
+int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s,
+                    bool tablesReady) {
   if (r.e1 <= r.e0) return kOk;
   if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
-  {
+  if (!tablesReady) {
     ProfScope ps__("k_normalize", s);
     k_normalize<<<r.e1 - r.e0, 256, 0, s>>>(a.elems, a.nDev, a.hist, a.probBits, es.table, r.e0);
   }

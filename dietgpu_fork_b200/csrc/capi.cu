@@ -147,12 +147,12 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   uint32_t* checksum = nullptr;
   const uint32_t* hist = histDev;
   const bool fused = !histDev && wl.totalTiles >= fusedMinTiles() && fusedCompressEnabled(); // histogram, tables, encoding and compaction in one launch
+  uint32_t* ownHist = nullptr;
   if (!hist) {
-    uint32_t* h = tmp.alloc<uint32_t>((size_t)num * 256);
+    ownHist = tmp.alloc<uint32_t>((size_t)num * 256);
     if (tmp.failed()) return kErrCuda;
-    DGB_CUDA(cudaMemsetAsync(h, 0, (size_t)num * 1024, s));
-    if (!fused && (rc = launchHistogram(elemsDev, num, wl.totalTiles, h, s))) return rc;
-    hist = h;
+    DGB_CUDA(cudaMemsetAsync(ownHist, 0, (size_t)num * 1024, s));
+    hist = ownHist;
   }
   if (useChecksum) {
     checksum = tmp.alloc<uint32_t>(num);
@@ -175,7 +175,11 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   EncodeScratch es;
   if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es, s))) return rc;
   if (fused) return launchFusedCompress(kFtNone, a, es, wl.totalTiles, nullptr, 0, s);
-  return launchAnsEncode(a, es, wholeRange(wl, num), s);
+  // separate launches: the histogram kernel also builds the tables (unless the caller supplied histograms)
+  if (ownHist && (rc = launchHistogram(elemsDev, num, wl.totalTiles, ownHist, s, es.fusedCtrl + kFusedCtrlFixed,
+                                       es.table, pb)))
+    return rc;
+  return launchAnsEncode(a, es, wholeRange(wl, num), s, ownHist != nullptr);
 }
 
 int ansDecode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t num, const void* const* in,
@@ -323,18 +327,20 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
       e0 = e1;
     }
   }
-  auto split = [&](const WorkRange& r, cudaStream_t st) {
+  auto split = [&](const WorkRange& r, cudaStream_t st, bool withTables) {
     return launchFloatSplit(ft, elemsDev, num, r.tile0, r.tile1, nDev, denseIn, plane, plane + planeBytes, hist,
-                            hist + (size_t)num * 256, checksum, useChecksum, st);
+                            hist + (size_t)num * 256, checksum, useChecksum, st,
+                            withTables ? es[0].fusedCtrl + kFusedCtrlFixed : nullptr, es[0].table,
+                            planes == 2 ? es[1].table : nullptr, pb);
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);
     if (planes == 1 && !nDev && !denseIn && num >= kFusedMinElems && wl.totalTiles >= fusedMinTiles() &&
         fusedCompressEnabled())
       return launchFusedCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
-    if ((rc = split(all, s))) return rc;
+    if ((rc = split(all, s, true))) return rc; // the split kernel also builds the encode tables
     for (int r = 0; r < planes; ++r)
-      if ((rc = launchAnsEncode(args[r], es[r], all, s))) return rc;
+      if ((rc = launchAnsEncode(args[r], es[r], all, s, true))) return rc;
     return kOk;
   }
   cudaEvent_t ev;
@@ -343,7 +349,7 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
   DGB_CUDA(cudaStreamWaitEvent(side, ev, 0));
   DGB_CUDA(cudaEventDestroy(ev));
   for (size_t g = 0; g < ranges.size(); ++g) {
-    if ((rc = split(ranges[g], side))) return rc;
+    if ((rc = split(ranges[g], side, false))) return rc;
     DGB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     DGB_CUDA(cudaEventRecord(ev, side));
     DGB_CUDA(cudaStreamWaitEvent(s, ev, 0));

@@ -2,6 +2,7 @@
 // range of 32768-word tiles. The per-tile work is splitTile in float_split.cuh.
 #include <cstdlib>
 
+#include "ans_encode.cuh"
 #include "float_split.cuh"
 #include "internal.h"
 #include "prof.h"
@@ -20,26 +21,44 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
   const uint32_t t0 = p.tileBegin + blockIdx.x * p.tilesPerCta;
   const uint32_t t1 = min(t0 + p.tilesPerCta, p.tileEnd);
   uint32_t cur = 0xffffffffu;
+  __shared__ uint32_t sLast;
+  // this CTA's counts of element `cur` go to the global bins; if they were the element's last, its table(s) follow
+  auto finishElement = [&]() {
+    __syncthreads();
+    splitHistFlush<256>(sh, p.hist0 + cur * 256, tid);
+    if (kPlanes == 2) splitHistFlush<256>(sh + kHistWords, p.hist1 + cur * 256, tid);
+    if (p.normTilesDone) {
+      const uint32_t eb = p.elems[cur].tileBase, ee = p.elems[cur + 1].tileBase;
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) {
+        const uint32_t count = min(t1, ee) - max(t0, eb);
+        sLast = atomicAdd(&p.normTilesDone[cur], count) + count == ee - eb ? 1u : 0u;
+      }
+      __syncthreads();
+      if (sLast) {
+        __threadfence();
+        const uint32_t total = p.nDev ? p.nDev[cur] : p.elems[cur].n;
+        normalizeElement<256>(p.hist0 + (size_t)cur * 256, total, p.normProbBits, p.normTable0 + (size_t)cur * 256, sh);
+        if (kPlanes == 2)
+          normalizeElement<256>(p.hist1 + (size_t)cur * 256, total, p.normProbBits, p.normTable1 + (size_t)cur * 256, sh);
+        __syncthreads();
+        for (uint32_t i = tid; i < 256 + 16; i += 256) sh[i] = 0; // the bins normalizeElement used as scratch
+      }
+    }
+    __syncthreads();
+  };
   for (uint32_t tile = t0; tile < t1; ++tile) {
     const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tile, cur);
     if (e != cur) {
-      if (cur != 0xffffffffu) {
-        __syncthreads();
-        splitHistFlush<256>(sh, p.hist0 + cur * 256, tid);
-        if (kPlanes == 2) splitHistFlush<256>(sh + kHistWords, p.hist1 + cur * 256, tid);
-        __syncthreads();
-      }
+      if (cur != 0xffffffffu) finishElement();
       cur = e;
     }
     const Elem el = p.elems[e];
     const uint32_t n = p.nDev ? p.nDev[e] : el.n;
     splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh);
   }
-  if (cur != 0xffffffffu) {
-    __syncthreads();
-    splitHistFlush<256>(sh, p.hist0 + cur * 256, tid);
-    if (kPlanes == 2) splitHistFlush<256>(sh + kHistWords, p.hist1 + cur * 256, tid);
-  }
+  if (cur != 0xffffffffu) finishElement();
 }
 
 template <int FT>
@@ -65,7 +84,8 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
 int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tileBegin, uint32_t tileEnd,
                      const uint32_t* nDev,
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
-                     uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s) {
+                     uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
+                     uint32_t* normTilesDone, uint2* normTable0, uint2* normTable1, int normProbBits) {
   if (tileEnd <= tileBegin) return kOk;
   SplitParams p;
   p.elems = elems;
@@ -81,6 +101,10 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
   p.hist1 = hist1;
   p.checksum = checksum;
   p.useChecksum = useChecksum;
+  p.normTilesDone = normTilesDone;
+  p.normTable0 = normTable0;
+  p.normTable1 = normTable1;
+  p.normProbBits = normProbBits;
   switch (ft) {
     case kFtF16: return launchSplitT<kFtF16>(p, s);
     case kFtBF16: return launchSplitT<kFtBF16>(p, s);

@@ -30,6 +30,12 @@ struct SplitParams {
   uint32_t* hist1;
   const uint32_t* checksum; // nullable
   int useChecksum;
+  // stand-alone kernel: when set, the CTA whose tiles complete an element's histogram(s) also builds its encode
+  // table(s) - the k_normalize launch disappears from small batches, which are launch-latency bound
+  uint32_t* normTilesDone;  // nullable; zeroed [numElems]
+  uint2* normTable0;        // [numElems][256]
+  uint2* normTable1;        // second exponent plane (fp64)
+  int normProbBits;
 };
 
 __device__ __forceinline__ void splitHistAdd(uint32_t* wh, uint32_t sym, uint32_t rep) {

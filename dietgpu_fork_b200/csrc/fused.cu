@@ -384,6 +384,9 @@ int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, ui
   p.sp.hist1 = nullptr;
   p.sp.checksum = checksum;
   p.sp.useChecksum = useChecksum;
+  p.sp.normTilesDone = nullptr;
+  p.sp.normTable0 = p.sp.normTable1 = nullptr;
+  p.sp.normProbBits = 0;
   p.splitCounter = es.fusedCtrl;
   p.splitCounterB = es.fusedCtrl + kFusedCtrlSplitB;
   p.smTicket = es.fusedCtrl + 1;

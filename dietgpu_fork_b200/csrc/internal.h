@@ -151,14 +151,18 @@ struct EncodeScratch {
 // totalGroups = number of 256-block size groups of the work list. Allocates and zeroes.
 int allocEncodeScratch(Temp& tmp, const EncodeArgs& a, uint32_t totalGroups, EncodeScratch& es, cudaStream_t s);
 // Enqueues normalise + encode + compaction for the elements of `r` on stream s.
-int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
+// tablesReady: the encode tables were already built by the histogram / split kernel (no k_normalize launch)
+int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s,
+                    bool tablesReady = false);
 // compaction only (k_coalesce), for callers that produced the block slots themselves
 int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
 // float split (ft == kFtNone: byte histogram of the raw input) + table normalisation + block encoding +
 // compaction in ONE persistent launch. Single-plane float types or raw ANS, host-known sizes, dense input (fused.cu).
 int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
                              const uint32_t* checksum, int useChecksum, cudaStream_t s);
-int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s);
+// normTilesDone (nullable, zeroed [numElems]): the CTA completing an element's histogram also builds its table
+int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s,
+                    uint32_t* normTilesDone = nullptr, uint2* normTable = nullptr, int normProbBits = 0);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or
 // output (useOut = 1); n = nDev[e] when given, else Elem::n. maxUnits bounds n.
 int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint32_t bytesPerUnit,
@@ -167,7 +171,9 @@ int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint
 int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tileBegin, uint32_t tileEnd,
                      const uint32_t* nDev,
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
-                     uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s);
+                     uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
+                     uint32_t* normTilesDone = nullptr, uint2* normTable0 = nullptr, uint2* normTable1 = nullptr,
+                     int normProbBits = 0);
 
 struct DecodeArgs {
   const Elem* elems; // device, numElems + 1 (tiles sized from capacities)
