@@ -336,7 +336,7 @@ __device__ __forceinline__ void writeChunkFull(uint32_t symAddr, uint32_t rawAdd
 }
 
 template <int PB, int FT>
-__global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 3 : 6) k_decode(const DecParams p) {
+__global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 4 : 6) k_decode(const DecParams p) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t kLut = 1u << PB;
   extern __shared__ __align__(128) uint8_t smemRaw[];
@@ -509,7 +509,7 @@ static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t smemBytes = decCtaSmem<PB, FT>();
   DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-  const uint32_t perSm = FT == kFtF64 ? 3u : 6u;
+  const uint32_t perSm = FT == kFtF64 ? 4u : 6u;
   uint32_t ctas = min(p.a.totalTiles, (uint32_t)smCount() * perSm);
   p.claimTiles = 1; // measured on B200 (bf16, 128 x 4 MiB): 1: 0.300, 2: 0.307, 3: 0.320, 4: 0.327 ms; static ranges: 0.359 ms
   if (const char* e = getenv("DGB_DEC_CLAIM")) p.claimTiles = (uint32_t)max(1, atoi(e)); // experiment knob
