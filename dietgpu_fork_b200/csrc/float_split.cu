@@ -18,9 +18,13 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
   for (uint32_t i = tid; i < kPlanes * kHistWords; i += 256) sh[i] = 0;
   __syncthreads();
 
-  const uint32_t t0 = p.tileBegin + blockIdx.x * p.tilesPerCta;
-  const uint32_t t1 = min(t0 + p.tilesPerCta, p.tileEnd);
-  uint32_t cur = 0xffffffffu;
+  // work units: whole tiles in a contiguous range per CTA, or tile slices dealt out round robin (SplitParams)
+  const uint32_t unitShift = p.unitShift, perTile = 1u << unitShift, unitWords = kTileSyms >> unitShift;
+  const uint32_t unitsTotal = (p.tileEnd - p.tileBegin) << unitShift;
+  const uint32_t u0 = p.roundRobin ? blockIdx.x : min(blockIdx.x * p.tilesPerCta, unitsTotal);
+  const uint32_t u1 = p.roundRobin ? unitsTotal : min(u0 + p.tilesPerCta, unitsTotal);
+  const uint32_t uStep = p.roundRobin ? gridDim.x : 1u;
+  uint32_t cur = 0xffffffffu, acc = 0; // element whose counts are in the bins, units of it done by this CTA
   __shared__ uint32_t sLast;
   // this CTA's counts of element `cur` go to the global bins; if they were the element's last, its table(s) follow
   auto finishElement = [&]() {
@@ -31,10 +35,7 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
       const uint32_t eb = p.elems[cur].tileBase, ee = p.elems[cur + 1].tileBase;
       __threadfence();
       __syncthreads();
-      if (tid == 0) {
-        const uint32_t count = min(t1, ee) - max(t0, eb);
-        sLast = atomicAdd(&p.normTilesDone[cur], count) + count == ee - eb ? 1u : 0u;
-      }
+      if (tid == 0) sLast = atomicAdd(&p.normTilesDone[cur], acc) + acc == (ee - eb) << unitShift ? 1u : 0u;
       __syncthreads();
       if (sLast) {
         __threadfence();
@@ -47,8 +48,10 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
       }
     }
     __syncthreads();
+    acc = 0;
   };
-  for (uint32_t tile = t0; tile < t1; ++tile) {
+  for (uint32_t u = u0; u < u1; u += uStep) {
+    const uint32_t tile = p.tileBegin + (u >> unitShift);
     const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tile, cur);
     if (e != cur) {
       if (cur != 0xffffffffu) finishElement();
@@ -56,7 +59,8 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
     }
     const Elem el = p.elems[e];
     const uint32_t n = p.nDev ? p.nDev[e] : el.n;
-    splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh);
+    splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh, unitWords, u & (perTile - 1u));
+    ++acc;
   }
   if (cur != 0xffffffffu) finishElement();
 }
@@ -73,6 +77,22 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
   uint32_t ctas = min(tiles, (uint32_t)smCount() * perSm);
   p.tilesPerCta = divUp(tiles, ctas);
   ctas = divUp(tiles, p.tilesPerCta);
+  p.unitShift = 0;
+  p.roundRobin = 0;
+  {
+    // few huge elements (every CTA gets at least a tile's worth of each element anyway, so the histogram flush
+    // per element change stays rare): half tiles round robin over a full grid. B200, bf16 1 x 256 MiB: contiguous
+    // ranges 123.7 us, round robin in units of 32768 / 16384 / 8192 / 4096 words 108.5 / 104.3 / 110.7 / 121.1 us
+    const uint32_t full = (uint32_t)smCount() * perSm;
+    bool rr = (uint64_t)tiles >= (uint64_t)full * p.numElems;
+    if (const char* e = getenv("DGB_SPLIT_RR")) rr = atoi(e) != 0; // experiment knob
+    if (rr) {
+      p.unitShift = 1;
+      if (const char* e = getenv("DGB_SPLIT_RR_SHIFT")) p.unitShift = (uint32_t)atoi(e);
+      p.roundRobin = 1;
+      ctas = min(tiles << p.unitShift, full);
+    }
+  }
   {
     ProfScope ps__("k_floatSplit", s);
     kern<<<ctas, 256, smemBytes, s>>>(p);

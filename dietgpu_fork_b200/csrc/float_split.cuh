@@ -22,6 +22,11 @@ struct SplitParams {
   uint32_t numElems;
   uint32_t tileBegin, tileEnd; // range of 32768-word tiles handled by this launch
   uint32_t tilesPerCta;
+  // stand-alone kernel, batches of few huge elements: work units of (tile >> unitShift) words dealt out round robin
+  // (unit u -> CTA u % grid), so that at any moment the CTAs stream one contiguous window of memory instead of one
+  // far-apart range each (DRAM efficiency); 0 / 0: contiguous ranges of whole tiles
+  uint32_t unitShift;
+  uint32_t roundRobin;
   const uint32_t* nDev;     // nullable (sparse: nnz)
   const uint8_t* denseIn;   // nullable: input rows at denseIn + planeOff * wordBytes (sparse)
   uint8_t* plane0;

@@ -198,7 +198,8 @@ size_t dgb_last_temp_bytes_used(void);
 /* ---- tuning ----------------------------------------------------------------------------------- */
 /* Compress chooses between two bit-identical schedules: one persistent fused launch (split or byte
  * histogram + table + encode + compaction) for batches of at least `tiles` 8-block tiles (32768 symbols
- * each), separate launches below. Default 1024 (measured cross-over on B200); 0 = always fused,
+ * each), separate launches below. Default: 1024 tiles with at least 16 elements, 2048 with at least 2,
+ * 8192 for a single element (measured cross-overs on B200); 0 = always fused,
  * a huge value = never, negative = back to the default. Process-wide; used by the parity tests to
  * cover both schedules at every size. */
 void dgb_set_fused_min_tiles(long long tiles);
