@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../../include/dietgpu_b200.h"
@@ -343,11 +344,14 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
       e0 = e1;
     }
   }
+  uint32_t minElemTiles = 0xffffffffu;
+  for (uint32_t i = 0; i < num; ++i)
+    minElemTiles = std::min(minElemTiles, wl.elems[i + 1].tileBase - wl.elems[i].tileBase);
   auto split = [&](const WorkRange& r, cudaStream_t st, bool withTables) {
     return launchFloatSplit(ft, elemsDev, num, r.tile0, r.tile1, nDev, denseIn, plane, plane + planeBytes, hist,
                             hist + (size_t)num * 256, checksum, useChecksum, st,
                             withTables ? es[0].fusedCtrl + kFusedCtrlFixed : nullptr, es[0].table,
-                            planes == 2 ? es[1].table : nullptr, pb);
+                            planes == 2 ? es[1].table : nullptr, pb, minElemTiles);
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);

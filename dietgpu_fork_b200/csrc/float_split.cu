@@ -20,10 +20,24 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
 
   // work units: whole tiles in a contiguous range per CTA, or tile slices dealt out round robin (SplitParams)
   const uint32_t unitShift = p.unitShift, perTile = 1u << unitShift, unitWords = kTileSyms >> unitShift;
-  const uint32_t unitsTotal = (p.tileEnd - p.tileBegin) << unitShift;
-  const uint32_t u0 = p.roundRobin ? blockIdx.x : min(blockIdx.x * p.tilesPerCta, unitsTotal);
-  const uint32_t u1 = p.roundRobin ? unitsTotal : min(u0 + p.tilesPerCta, unitsTotal);
-  const uint32_t uStep = p.roundRobin ? gridDim.x : 1u;
+  uint32_t unitsTotal = (p.tileEnd - p.tileBegin) << unitShift;
+  uint32_t u0 = p.roundRobin ? blockIdx.x : min(blockIdx.x * p.tilesPerCta, unitsTotal);
+  uint32_t u1 = p.roundRobin ? unitsTotal : min(u0 + p.tilesPerCta, unitsTotal);
+  uint32_t uStep = p.roundRobin ? gridDim.x : 1u;
+  if (p.roundRobin == 2) {
+    // round robin per element: CTA b starts at tile floor(b * tiles / grid); the CTAs whose start falls into one
+    // element share that element (every element is at least tiles / grid tiles long, checked by the host), so a
+    // CTA flushes its histogram once and every element is swept by one contiguous front
+    const uint32_t tiles = p.tileEnd - p.tileBegin, grid = gridDim.x;
+    const uint32_t tb = (uint32_t)((uint64_t)blockIdx.x * tiles / grid);
+    const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, p.tileBegin + tb, 0);
+    const uint32_t eb = p.elems[e].tileBase - p.tileBegin, ee = p.elems[e + 1].tileBase - p.tileBegin;
+    const uint32_t b0 = (uint32_t)(((uint64_t)eb * grid + tiles - 1) / tiles);
+    const uint32_t b1 = min(grid, (uint32_t)(((uint64_t)ee * grid + tiles - 1) / tiles));
+    u0 = (eb << unitShift) + (blockIdx.x - b0);
+    u1 = ee << unitShift;
+    uStep = b1 - b0;
+  }
   uint32_t cur = 0xffffffffu, acc = 0; // element whose counts are in the bins, units of it done by this CTA
   __shared__ uint32_t sLast;
   // this CTA's counts of element `cur` go to the global bins; if they were the element's last, its table(s) follow
@@ -91,6 +105,17 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
       if (const char* e = getenv("DGB_SPLIT_RR_SHIFT")) p.unitShift = (uint32_t)atoi(e);
       p.roundRobin = 1;
       ctas = min(tiles << p.unitShift, full);
+    } else {
+      // several elements, each long enough to get CTAs of its own: round robin inside every element
+      bool per = p.tileBegin == 0 && p.minElemTiles >= 2 * divUp(tiles, min(tiles, full)) && tiles >= full;
+      if (const char* e = getenv("DGB_SPLIT_RR_ELEM")) per = per && atoi(e) != 0; // experiment knob
+      if (per) {
+        p.unitShift = 1; // at least four units per CTA, so that the CTAs of an element finish together
+        while (p.unitShift < 3 && ((uint64_t)tiles << p.unitShift) < 4ull * full) ++p.unitShift;
+        if (const char* e = getenv("DGB_SPLIT_RR_SHIFT")) p.unitShift = (uint32_t)atoi(e);
+        p.roundRobin = 2;
+        ctas = full;
+      }
     }
   }
   {
@@ -105,7 +130,8 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
                      const uint32_t* nDev,
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
-                     uint32_t* normTilesDone, uint2* normTable0, uint2* normTable1, int normProbBits) {
+                     uint32_t* normTilesDone, uint2* normTable0, uint2* normTable1, int normProbBits,
+                     uint32_t minElemTiles) {
   if (tileEnd <= tileBegin) return kOk;
   SplitParams p;
   p.elems = elems;
@@ -125,6 +151,7 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
   p.normTable0 = normTable0;
   p.normTable1 = normTable1;
   p.normProbBits = normProbBits;
+  p.minElemTiles = minElemTiles;
   switch (ft) {
     case kFtF16: return launchSplitT<kFtF16>(p, s);
     case kFtBF16: return launchSplitT<kFtBF16>(p, s);

@@ -26,7 +26,8 @@ struct SplitParams {
   // (unit u -> CTA u % grid), so that at any moment the CTAs stream one contiguous window of memory instead of one
   // far-apart range each (DRAM efficiency); 0 / 0: contiguous ranges of whole tiles
   uint32_t unitShift;
-  uint32_t roundRobin;
+  uint32_t roundRobin;   // 1: over the whole work list, 2: inside every element (see k_floatSplit)
+  uint32_t minElemTiles; // host hint: tiles of the shortest element (0: unknown)
   const uint32_t* nDev;     // nullable (sparse: nnz)
   const uint8_t* denseIn;   // nullable: input rows at denseIn + planeOff * wordBytes (sparse)
   uint8_t* plane0;

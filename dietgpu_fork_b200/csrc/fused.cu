@@ -378,6 +378,7 @@ int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, ui
   p.sp.tilesPerCta = 1;
   p.sp.unitShift = 0;
   p.sp.roundRobin = 0;
+  p.sp.minElemTiles = 0;
   p.sp.nDev = nullptr;
   p.sp.denseIn = nullptr;
   p.sp.plane0 = (uint8_t*)a.planeBase;

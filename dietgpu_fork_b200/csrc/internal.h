@@ -173,7 +173,7 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
                      uint32_t* normTilesDone = nullptr, uint2* normTable0 = nullptr, uint2* normTable1 = nullptr,
-                     int normProbBits = 0);
+                     int normProbBits = 0, uint32_t minElemTiles = 0);
 
 struct DecodeArgs {
   const Elem* elems; // device, numElems + 1 (tiles sized from capacities)
