@@ -238,8 +238,9 @@ cudaStream_t sideStream() {
 
 // DGB_FUSED=0 selects the separate split / normalise / encode launches (kept for the sparse and fp64 paths).
 // The fused persistent kernel pays a start-up bubble (encode warps wait for the first element's table) and a
-// compaction tail; measured on B200 it wins from about 1024 8-block tiles (32 MiB of symbols) upwards and loses
-// below (bf16 16 x 1 MiB: 0.068 ms fused vs 0.048 ms as separate launches; 32 x 2 MiB: 0.107 vs 0.112).
+// compaction tail; measured on B200 it loses below about 1024 8-block tiles (32 MiB of symbols; bf16 16 x 1 MiB:
+// 0.068 ms fused vs 0.048 ms as separate launches) and, above that, wins when there are elements to overlap
+// (fusedWanted below).
 constexpr uint32_t kFusedMinElems = 1;
 static long long g_fusedMinTiles = -1; // < 0: default (or DGB_FUSED_MIN_TILES); set by dgb_set_fused_min_tiles
 uint32_t fusedMinTiles() {

@@ -14,7 +14,7 @@
 //     exponent bytes into the plane; the histogram stays in the CTA's shared-memory bins while its claims stay
 //     inside one element and is added to the element's global bins when the CTA moves on; the CTA whose slice
 //     count completes an element normalises its table and publishes the element's ready flag (release);
-//   * encode warps claim runs of 4 blocks in the same order, wait (acquire) for the run's element, and encode
+//   * encode warps claim runs of 2 blocks (1 for small batches) in the same order, wait (acquire) for the run's element, and encode
 //     exactly as the stand-alone kernel does (encodeRun in ans_encode.cuh);
 //   * a split CTA that finds no tile left becomes an encode CTA;
 //   * compaction (what k_coalesce does for the stand-alone encoder) is the warps' last job: every finished block
