@@ -104,6 +104,24 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def pin_to_gpu_numa_node(index):
+    """Runs this rank on the CPUs next to its GPU (NVML's ideal affinity), so that the pinned host buffers of the
+    host-buffer leg are first touched, hence placed, on the GPU's own NUMA node. Both arms do this; without it
+    the ranks of a multi-GPU run land on arbitrary nodes and share one memory controller."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def make_batch(rank):
     torch.manual_seed(2000 + rank)
     ts = []
@@ -200,6 +218,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
     torch.cuda.set_device(local_rank)
+    pin_to_gpu_numa_node(local_rank)
     dist = None
     if world > 1 and (args.impl == "ours" or ref.ok()):
         # the reference's CUDA build shards the batch exactly like ours: one rank per GPU for both arms
