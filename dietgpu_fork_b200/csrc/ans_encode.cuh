@@ -179,7 +179,10 @@ constexpr uint32_t kEncChunk = kEncChunkRows * 32;
 inline uint32_t chooseRunShift(uint32_t totalTiles, uint32_t warpsWanted) {
   uint32_t shift = 2;
   if (const char* e = getenv("DGB_RUN_SHIFT")) return (uint32_t)atoi(e); // experiment knob
-  while (shift < 3 && (totalTiles << shift) < warpsWanted) ++shift;
+  // single blocks until every warp gets about four runs: with fewer, the last round of 2-block runs leaves most
+  // warps idle (B200, bf16, fused, 2- vs 1-block runs: 8 x 16 MiB 0.175 / 0.160 ms, 16 x 8 MiB 0.167 / 0.155,
+  // 32 x 8 MiB 0.253 / 0.241, 4 x 64 MiB 0.266 / 0.273, 128 x 4 MiB 0.422 / 0.428)
+  while (shift < 3 && ((uint64_t)totalTiles << shift) < 4ull * warpsWanted) ++shift;
   return shift;
 }
 constexpr uint32_t kBlockChunks = kBlockSyms / kEncChunk;
