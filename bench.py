@@ -197,6 +197,16 @@ def cpu_oracle_roundtrip(sample_elems, budget_s=15.0):
                                              f"compress+decompress, {reps} pass(es), {threads} OpenMP threads")
 
 
+def cpu_model():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip() + f" ({os.cpu_count()} logical CPUs)"
+    except Exception:
+        pass
+    return "unknown"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -204,6 +214,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (kernel sweeps only)")
+    ap.add_argument("--no-collective", action="store_true", help="N > 1: skip the compressed-collective record")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -223,25 +235,35 @@ def main():
     if world > 1 and (args.impl == "ours" or ref.ok()):
         # the reference's CUDA build shards the batch exactly like ours: one rank per GPU for both arms
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank),
+                                timeout=datetime.timedelta(seconds=300))
 
     if args.impl == "reference" and not ref.ok():
         return reference_cpu_arm(args)
 
-    from dietgpu_fork_b200 import _capi, codec, torch_ops
+    # The reference arm must not load the repo's library: everything it needs comes from oracle/_ref.
+    if ref is None:
+        from dietgpu_fork_b200 import _capi, codec
+        max_bytes = codec.get_max_float_compressed_size(BF16, ELEM_WORDS)
+    else:
+        _capi = codec = None
+        ref.lib.ref_float_max_compressed_size.restype = C.c_uint32
+        max_bytes = ref.lib.ref_float_max_compressed_size(BF16, C.c_uint32(ELEM_WORDS))
 
     ins = make_batch(rank)
     U = BATCH * ELEM_WORDS * 2
-    max_bytes = codec.get_max_float_compressed_size(BF16, ELEM_WORDS)
     comp = torch.empty((BATCH, max_bytes), dtype=torch.uint8, device="cuda")
     rows = [comp[i] for i in range(BATCH)]
     sizes = torch.zeros(BATCH, dtype=torch.int32, device="cuda")
     outs = [torch.empty(ELEM_WORDS, dtype=torch.bfloat16, device="cuda") for _ in range(BATCH)]
     ok = torch.zeros(BATCH, dtype=torch.uint8, device="cuda")
     dsizes = torch.zeros(BATCH, dtype=torch.int32, device="cuda")
-    temp_bytes = max(_capi.lib.dgb_temp_bytes_required(2, BF16, BATCH, ELEM_WORDS),
-                     _capi.lib.dgb_temp_bytes_required(3, BF16, BATCH, ELEM_WORDS))
-    temp = torch.empty(temp_bytes, dtype=torch.uint8, device="cuda")
+    temp = None
+    if ref is None:
+        temp_bytes = max(_capi.lib.dgb_temp_bytes_required(2, BF16, BATCH, ELEM_WORDS),
+                         _capi.lib.dgb_temp_bytes_required(3, BF16, BATCH, ELEM_WORDS))
+        temp = torch.empty(temp_bytes, dtype=torch.uint8, device="cuda")
 
     if ref is not None:
         def do_compress():
@@ -268,15 +290,17 @@ def main():
     # correctness inside the bench: the round trip must be bit exact
     csz = sizes.cpu().numpy().astype(np.int64)
     assert ok.cpu().numpy().all(), "decompress reported failure"
-    for i in (0, BATCH // 2, BATCH - 1):
-        assert torch.equal(outs[i].view(torch.int16), ins[i].view(torch.int16)), "round trip mismatch"
+    for i in range(BATCH):  # every element, bit for bit
+        assert torch.equal(outs[i].view(torch.int16), ins[i].view(torch.int16)), f"round trip mismatch in element {i}"
+    assert dsizes.cpu().tolist() == [ELEM_WORDS] * BATCH, "decoded sizes"
     C_total = int(csz.sum())
     ratio = C_total / U
 
     sampler = ClockSampler(local_rank)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-    launches0 = _capi.lib.dgb_profile_launches()
+    launches0 = 0
     if ref is None:
+        launches0 = _capi.lib.dgb_profile_launches()
         _capi.lib.dgb_profile_enable(1)
     barrier()
     sampler.start()
@@ -298,9 +322,10 @@ def main():
     for a, b, c in pairs:
         t_c += a.elapsed_time(b)
         t_d += b.elapsed_time(c)
-    launches = _capi.lib.dgb_profile_launches() - launches0
+    launches = 0
     kern = {}
     if ref is None:
+        launches = _capi.lib.dgb_profile_launches() - launches0
         _capi.lib.dgb_profile_enable(0)
         buf = C.create_string_buffer(1 << 16)
         _capi.lib.dgb_profile_report(buf, len(buf))
@@ -351,7 +376,10 @@ def main():
     }
 
     # ---------------- e2e: host buffers through the public op API ----------------
-    e2e = run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks)
+    e2e = None if args.no_e2e else run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks)
+    collective = None
+    if ref is None and dist is not None and not args.no_collective:
+        collective = run_collectives(dist, rank, world)
 
     if rank != 0:
         if dist is not None:
@@ -371,6 +399,8 @@ def main():
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
         "roofline": roofline, "phases": phase,
     }
+    if collective is not None:
+        line["collective"] = collective
     if args.impl == "reference":
         line["impl"] = "reference"
         line["reference_kind"] = "reference CUDA build (oracle/_ref/libdietgpu_ref.so) on the GPU"
@@ -381,11 +411,41 @@ def main():
     elif n_ranks == 1 and not args.no_cpu_baseline:
         v, threads, desc = cpu_oracle_roundtrip(min(BATCH, 16))
         line["cpu_baseline"] = {"value": round(v, 3), "unit": "GB/s", "cores": threads, "kind": "port",
-                                "sample": desc}
+                                "sample": desc, "cpu": cpu_model()}
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def pcie_duplex_gbs(nbytes=256 << 20, chunk=32 << 20):
+    """Host<->device link rate per direction with both directions busy (pinned memory, 32 MiB copies on two
+    streams; scripts/pcie_probe.py is the long form). Measured in the same run, on this rank, so that the e2e
+    number can be read as a fraction of what the link allows."""
+    h_in = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d_a = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    d_b = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    best = None
+    for _ in range(4):
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        s1.wait_stream(torch.cuda.current_stream())
+        s2.wait_stream(torch.cuda.current_stream())
+        for off in range(0, nbytes, chunk):
+            with torch.cuda.stream(s1):
+                d_a[off:off + chunk].copy_(h_in[off:off + chunk], non_blocking=True)
+            with torch.cuda.stream(s2):
+                h_out[off:off + chunk].copy_(d_b[off:off + chunk], non_blocking=True)
+        torch.cuda.current_stream().wait_stream(s1)
+        torch.cuda.current_stream().wait_stream(s2)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        best = ms if best is None else min(best, ms)
+    return nbytes / best / 1e6
 
 
 def run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks):
@@ -396,10 +456,13 @@ def run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks):
                which pipeline H2D / kernels / D2H over element groups inside the library (csrc/host_pipe.cu).
     reference  its API takes device pointers only, so the caller does what its users do: copy the batch in,
                floatCompress, read the sizes, copy the archives out (exact sizes); copy them back in,
-               floatDecompress, copy the tensors out.
+               floatDecompress, copy the tensors out. (Nothing of this repo's library is loaded on that arm.)
     `unpipelined` is that same plain sequence around OUR device-pointer calls, to separate what the pipelining
-    buys from what the kernels buy (PCIe dominates both)."""
-    from dietgpu_fork_b200 import codec
+    buys from what the kernels buy (PCIe dominates both). Every number is the median of 3 repeats of >= 20 steps;
+    `pcie_bound` is the same metric if the step ran at the duplex link rate measured in this run."""
+    codec = None
+    if ref is None:
+        from dietgpu_fork_b200 import codec
     U = BATCH * ELEM_WORDS * 2
     max_bytes = comp.shape[1]
     host_in = torch.empty((BATCH, ELEM_WORDS), dtype=torch.bfloat16).pin_memory()
@@ -438,43 +501,73 @@ def run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks):
         c = sum(csz)
         copied["h2d"], copied["d2h"] = U + c, c + U + 2 * BATCH * 4 + BATCH
 
-    def timed(step, steps):
-        step()
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-        host_out.zero_()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(steps):
-            step()
-        b.record()
-        torch.cuda.synchronize()
-        ms = a.elapsed_time(b)
-        if dist is not None:
-            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = t.item()
-        assert torch.equal(host_out.view(torch.int16), host_in.view(torch.int16)), "e2e round trip mismatch"
-        return n_ranks * 2.0 * U / (ms / steps * 1e-3) / 1e9
+    steps = max(20, args.steps)
+    repeats = 3
 
-    steps = max(2, min(args.steps, 5))
+    def timed(step):
+        step()
+        vals = []
+        for _ in range(repeats):
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            torch.cuda.synchronize()
+            host_out.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(steps):
+                step()
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b)
+            if dist is not None:
+                t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = t.item()
+            assert torch.equal(host_out.view(torch.int16), host_in.view(torch.int16)), "e2e round trip mismatch"
+            vals.append(n_ranks * 2.0 * U / (ms / steps * 1e-3) / 1e9)
+        return float(np.median(vals)), vals
+
+    link = pcie_duplex_gbs()
+    if dist is not None:  # the slowest rank's link bounds the job
+        t = torch.tensor([link], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        link = t.item()
+
+    def bound(h2d, d2h):  # GB/s of the metric if both copy directions ran at the duplex link rate, nothing else
+        return n_ranks * 2.0 * U / (max(h2d, d2h) / (link * 1e9)) / 1e9
+
     if ref is not None:
-        v = timed(lambda: plain_step(ref.compress, ref.decompress), steps)
+        v, vals = timed(lambda: plain_step(ref.compress, ref.decompress))
         return {"value": round(v, 2), "unit": "GB/s", "h2d_bytes_per_step": copied["h2d"],
-                "d2h_bytes_per_step": copied["d2h"], "steps": steps,
+                "d2h_bytes_per_step": copied["d2h"], "steps": steps, "repeats": [round(x, 2) for x in vals],
+                "pcie_duplex_GBps_per_direction": round(link, 1),
+                "pcie_bound": round(bound(copied["h2d"], copied["d2h"]), 2),
                 "path": "H2D, floatCompress, sizes D2H, archives D2H, archives H2D, floatDecompress, D2H "
                         "(the reference API takes device pointers only)"}
-    plain = timed(lambda: plain_step(
+    plain, _ = timed(lambda: plain_step(
         lambda i, o, s: codec.float_compress(BF16, i, o, s, 10, False, temp=temp),
-        lambda i, o, k, s: codec.float_decompress(BF16, i, o, k, s, 10, False, temp=temp)), steps)
-    v = timed(pipelined_step, steps)
+        lambda i, o, k, s: codec.float_decompress(BF16, i, o, k, s, 10, False, temp=temp)))
+    v, vals = timed(pipelined_step)
+    pb = bound(copied["h2d"], copied["d2h"])
     return {"value": round(v, 2), "unit": "GB/s", "h2d_bytes_per_step": copied["h2d"],
-            "d2h_bytes_per_step": copied["d2h"], "steps": steps,
+            "d2h_bytes_per_step": copied["d2h"], "steps": steps, "repeats": [round(x, 2) for x in vals],
+            "pcie_duplex_GBps_per_direction": round(link, 1), "pcie_bound": round(pb, 2),
+            "frac_of_pcie_bound": round(v / pb, 3),
             "path": "dgb_float_compress_host + dgb_float_decompress_host (copies and kernels pipelined over "
                     "element groups inside the call)",
             "unpipelined": round(plain, 2)}
+
+
+def run_collectives(dist, rank, world):
+    """BASELINE configs[4] next to the sharded number: compressed all-gather / all-to-all of 64 MiB of bf16 per rank
+    against the uncompressed NCCL collectives (scripts/bench_collectives.py; bit equality asserted inside)."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import bench_collectives
+    try:
+        return bench_collectives.measure(dist, rank, world, mib=64, steps=10, warmup=3, chunks=1)
+    except Exception as e:  # the sharded line must not be lost to a collective failure; say what happened
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def reference_cpu_arm(args):

@@ -48,16 +48,29 @@ def _ptrs(ts):
     return _capi.ptr_array([t.data_ptr() for t in ts])
 
 
+def _bound(v, what, size):
+    # the library returns 0 when the bound does not fit the 32-bit API (the reference CHECK-aborts / wraps there)
+    if v == 0 and size > 0:
+        raise ValueError(f"{what}: {size} is too large for the 32-bit size API")
+    return v
+
+
 def get_max_compressed_size(uncompressed_bytes):
-    return lib.dgb_ans_max_compressed_size(uncompressed_bytes)
+    if not 0 <= uncompressed_bytes <= 0xFFFFFFFF:
+        raise ValueError(f"getMaxCompressedSize: {uncompressed_bytes} is out of range")
+    return _bound(lib.dgb_ans_max_compressed_size(uncompressed_bytes), "getMaxCompressedSize", uncompressed_bytes)
 
 
 def get_max_float_compressed_size(float_type, size):
-    return lib.dgb_float_max_compressed_size(float_type, size)
+    if not 0 <= size <= 0xFFFFFFFF:
+        raise ValueError(f"getMaxFloatCompressedSize: {size} is out of range")
+    return _bound(lib.dgb_float_max_compressed_size(float_type, size), "getMaxFloatCompressedSize", size)
 
 
 def get_max_sparse_float_compressed_size(float_type, size):
-    return lib.dgb_sparse_float_max_compressed_size(float_type, size)
+    if not 0 <= size <= 0xFFFFFFFF:
+        raise ValueError(f"getMaxSparseFloatCompressedSize: {size} is out of range")
+    return _bound(lib.dgb_sparse_float_max_compressed_size(float_type, size), "getMaxSparseFloatCompressedSize", size)
 
 
 def last_temp_bytes_used():
@@ -91,6 +104,30 @@ def ans_decode_batch_pointer(ins, outs, out_success=None, out_sizes=None, prob_b
                                           _capi.u32_array(caps), _ptr(out_success), _ptr(out_sizes),
                                           _stream(stream), mm, n, C.byref(nm))
     if _capi.check(rc, "ansDecodeBatchPointer"):
+        _raise_mismatch(mm, nm)
+
+
+def ans_encode_batch_stride(in_dev, num, in_size, in_stride, out_dev, out_stride, out_sizes, prob_bits=10,
+                            use_checksum=False, histogram=None, temp=None, stream=None):
+    """ansEncodeBatchStride (dietgpu/ans/GpuANSCodec.h:68-98): `num` inputs of `in_size` bytes, `in_stride` bytes
+    apart in the device tensor `in_dev`; archives `out_stride` bytes apart in `out_dev`."""
+    tp, tb = _temp(temp)
+    rc = lib.dgb_ans_encode_batch_stride(tp, tb, prob_bits, int(use_checksum), num, _ptr(in_dev), in_size,
+                                         in_stride, _ptr(histogram), _ptr(out_dev), out_stride, _ptr(out_sizes),
+                                         _stream(stream))
+    _capi.check(rc, "ansEncodeBatchStride")
+
+
+def ans_decode_batch_stride(in_dev, num, in_stride, out_dev, out_stride, out_capacity, out_success=None,
+                            out_sizes=None, prob_bits=10, use_checksum=False, temp=None, stream=None):
+    """ansDecodeBatchStride (dietgpu/ans/GpuANSCodec.h:222-257)."""
+    tp, tb = _temp(temp)
+    mm = (C.c_uint32 * max(num, 1))()
+    nm = C.c_uint32(0)
+    rc = lib.dgb_ans_decode_batch_stride(tp, tb, prob_bits, int(use_checksum), num, _ptr(in_dev), in_stride,
+                                         _ptr(out_dev), out_stride, out_capacity, _ptr(out_success),
+                                         _ptr(out_sizes), _stream(stream), mm, num, C.byref(nm))
+    if _capi.check(rc, "ansDecodeBatchStride"):
         _raise_mismatch(mm, nm)
 
 

@@ -15,6 +15,7 @@
 
 #include "float_math.cuh"
 #include "internal.h"
+#include "knobs.h"
 #include "prof.h"
 
 namespace dgb {
@@ -66,6 +67,9 @@ __global__ void __launch_bounds__(256) k_decodePrep(const DecodeArgs a, DecInfo*
   const uint32_t nb = ok ? ah[1] : 0;
   const uint32_t pb = ok ? (ah[4] & 0xfu) : (uint32_t)a.probBits;
   if (ok && (int)pb != a.probBits) ok = false;
+  // the block count is implied by the symbol count: a header that disagrees would make k_decode index past the
+  // caller's capacity (the reference only asserts, dietgpu/ans/GpuANSDecode.cuh:325-341)
+  if (ok && nb != divUp(n, kBlockSyms)) ok = false;
   if (s == 0) {
     DecInfo d;
     d.ans = ans;
@@ -73,7 +77,7 @@ __global__ void __launch_bounds__(256) k_decodePrep(const DecodeArgs a, DecInfo*
     d.nb = ok ? nb : 0;
     d.n = ok ? n : 0;
     d.ok = ok;
-    d.pad = 0;
+    d.totalWords = ok ? ah[3] : 0;
     info[plane * a.numElems + e] = d;
     if (plane == 0) {
       if (a.outSuccess) a.outSuccess[e] = ok ? 1 : 0;
@@ -396,17 +400,38 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 4 : 6) k_decode
     const Elem el = a.elems[e];
     const uint32_t blk = (tile - el.tileBase) * kTileBlocks + w;
     if (!d0.ok || blk >= d0.nb) continue;
+    if constexpr (kPlanes == 2) {
+      if (!p.info[a.numElems + e].ok) { // the second exponent plane's header is bad: nothing of this element decodes
+        if (lane == 0 && blk == 0 && a.outSuccess) a.outSuccess[e] = 0;
+        continue;
+      }
+    }
     const uint32_t nb = d0.nb;
 
-    uint32_t blkLen = 0;
+    // Block index entries come from the archive: an entry that disagrees with what the header implies (symbols of
+    // the block, 16-byte aligned start inside the payload) would turn into a misaligned or out-of-bounds bulk
+    // copy; such a block is skipped and the element reported as failed.
+    const uint32_t blkLen = min(kBlockSyms, d0.n - blk * kBlockSyms);
+    bool sane = true;
+#pragma unroll
+    for (int pl = 0; pl < kPlanes; ++pl) {
+      const DecInfo dp = pl == 0 ? d0 : p.info[a.numElems + e];
+      const uint2 bw = ((const uint2*)(dp.ans + kAnsFixedBytes + 128u * nb))[blk];
+      const uint32_t words = bw.x & 0xffffu;
+      sane = sane && (bw.x >> 16) == blkLen && words <= kStageWords && (bw.y & 7u) == 0 &&
+             (uint64_t)bw.y + roundUp(words, 8) <= dp.totalWords;
+    }
+    if (!sane) {
+      if (lane == 0 && a.outSuccess) a.outSuccess[e] = 0;
+      continue;
+    }
 #pragma unroll
     for (int pl = 0; pl < kPlanes; ++pl) {
       const uint8_t* ans = pl == 0 ? d0.ans : p.info[a.numElems + e].ans;
       DecCtx& c = ctx[pl];
       c.state = ((const uint32_t*)(ans + kAnsFixedBytes))[blk * 32 + lane];
       const uint2 bw = ((const uint2*)(ans + kAnsFixedBytes + 128u * nb))[blk];
-      blkLen = min(bw.x >> 16, kBlockSyms);
-      const uint32_t words = min(bw.x & 0xffffu, kStageWords);
+      const uint32_t words = bw.x & 0xffffu;
       c.src = ans + ansOverhead(nb) + 2 * (size_t)bw.y;
       c.totalBytes = roundUp(words, 8) * 2;
       c.ptrBytes = words * 2;
@@ -508,11 +533,18 @@ template <int PB, int FT>
 static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t smemBytes = decCtaSmem<PB, FT>();
-  DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  {
+    static DeviceOnce once;
+    const int dev = currentDevice();
+    if (once.first(dev)) {
+      DGB_CUDA(cudaFuncSetAttribute(k_decode<PB, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+      once.done(dev);
+    }
+  }
   const uint32_t perSm = FT == kFtF64 ? 4u : 6u;
   uint32_t ctas = min(p.a.totalTiles, (uint32_t)smCount() * perSm);
   p.claimTiles = 1; // measured on B200 (bf16, 128 x 4 MiB): 1: 0.300, 2: 0.307, 3: 0.320, 4: 0.327 ms; static ranges: 0.359 ms
-  if (const char* e = getenv("DGB_DEC_CLAIM")) p.claimTiles = (uint32_t)max(1, atoi(e)); // experiment knob
+  if (DGB_KNOB("DGB_DEC_CLAIM", 0) > 0) p.claimTiles = (uint32_t)DGB_KNOB("DGB_DEC_CLAIM", 0); // experiment knob
   if (p.a.totalTiles < ctas * p.claimTiles) p.claimTiles = 1;
   ctas = min(ctas, divUp(p.a.totalTiles, p.claimTiles));
   {

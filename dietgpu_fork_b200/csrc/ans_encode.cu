@@ -14,19 +14,27 @@
 
 #include "ans_encode.cuh"
 #include "internal.h"
+#include "knobs.h"
 #include "prof.h"
 
 namespace dgb {
 
+int currentDevice() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev < 0 ? 0 : (dev >= kMaxDevices ? kMaxDevices - 1 : dev);
+}
+
 int smCount() {
-  static int cached = 0;
-  if (!cached) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-    if (cached <= 0) cached = 148;
+  static int cached[kMaxDevices] = {}; // written once per device with the same value: a race is benign
+  const int dev = currentDevice();
+  int v = __atomic_load_n(&cached[dev], __ATOMIC_RELAXED);
+  if (!v) {
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    if (v <= 0) v = 148;
+    __atomic_store_n(&cached[dev], v, __ATOMIC_RELAXED);
   }
-  return cached;
+  return v;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -370,12 +378,18 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   p.runShift = chooseRunShift(r.tile1 - r.tile0, (uint32_t)smCount() * kEncCtasPerSm * kEncWarps);
   const uint32_t runs = (r.tile1 - r.tile0) << p.runShift;
   uint32_t perSm = kEncCtasPerSm;
-  if (const char* e = getenv("DGB_ENC_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
+  if (DGB_KNOB("DGB_ENC_CTAS", 0) > 0) perSm = (uint32_t)DGB_KNOB("DGB_ENC_CTAS", 0); // experiment knob
   const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * perSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
   auto launch = [&](auto kern) -> int {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    static DeviceOnce onceByPb[3]; // the three instantiations share one function-pointer type
+    DeviceOnce& once = onceByPb[a.probBits - 9];
+    const int dev = currentDevice();
+    if (once.first(dev)) {
+      DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+      once.done(dev);
+    }
     {
       ProfScope ps__("k_encode", s);
       kern<<<grid, kEncWarps * 32, smemBytes, s>>>(p);

@@ -6,6 +6,7 @@
 
 #include "common.cuh"
 #include "internal.h"
+#include "knobs.h"
 
 namespace dgb {
 
@@ -178,7 +179,7 @@ constexpr uint32_t kEncChunk = kEncChunkRows * 32;
 // tail: a run then takes ~100 us of wall time with 40 warps per SM; fused kernel 0.42 ms vs 0.386 ms.)
 inline uint32_t chooseRunShift(uint32_t totalTiles, uint32_t warpsWanted) {
   uint32_t shift = 2;
-  if (const char* e = getenv("DGB_RUN_SHIFT")) return (uint32_t)atoi(e); // experiment knob
+  if (DGB_KNOB("DGB_RUN_SHIFT", -1) >= 0) return (uint32_t)DGB_KNOB("DGB_RUN_SHIFT", -1); // experiment knob
   // single blocks until every warp gets about four runs: with fewer, the last round of 2-block runs leaves most
   // warps idle (B200, bf16, fused, 2- vs 1-block runs: 8 x 16 MiB 0.175 / 0.160 ms, 16 x 8 MiB 0.167 / 0.155,
   // 32 x 8 MiB 0.253 / 0.241, 4 x 64 MiB 0.266 / 0.273, 128 x 4 MiB 0.422 / 0.428)

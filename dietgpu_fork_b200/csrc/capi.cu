@@ -12,6 +12,7 @@
 
 #include "../../include/dietgpu_b200.h"
 #include "internal.h"
+#include "knobs.h"
 #include "prof.h"
 
 namespace dgb {
@@ -24,6 +25,22 @@ int launchSparseScatter(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
 namespace {
 
 bool validFloatType(int ft) { return ft >= kFtF16 && ft <= kFtF64; }
+
+uint64_t ansMaxBytes64(uint64_t n);
+uint64_t floatMaxBytes64(int ft, uint64_t n);
+// every element must have a size bound the 32-bit API can express (see dgb_*_max_compressed_size)
+bool ansSizesOk(uint32_t num, const uint32_t* n) {
+  for (uint32_t i = 0; i < num; ++i)
+    if (ansMaxBytes64(n[i]) > 0x7fffffffull) return false;
+  return true;
+}
+bool floatSizesOk(int ft, uint32_t num, const uint32_t* n, uint64_t extra = 0) {
+  for (uint32_t i = 0; i < num; ++i) {
+    const uint64_t f = floatMaxBytes64(ft, n[i]);
+    if (f > 0xffffffffull || f + extra + n[i] / 8 > 0xffffffffull) return false;
+  }
+  return true;
+}
 
 // Host-side work list: tiles of `tileUnits` symbols/words per element, at least one per element.
 struct WorkList {
@@ -75,11 +92,63 @@ WorkRange wholeRange(const WorkList& wl, uint32_t num) {
   return WorkRange{0, num, 0, wl.totalTiles, 0, wl.totalBlocks};
 }
 
+// Descriptor tables travel through a small per-thread ring of pinned staging buffers, so that the H2D copy is a
+// true asynchronous DMA from memory that outlives the call (a pageable source is staged synchronously by the
+// runtime, and would be a use-after-free if that ever changed). A slot is reused only after the copy that last
+// read it has completed (event). The calls read the caller's host arrays at call time, so they are NOT capturable
+// into CUDA graphs (neither are the reference's).
+struct PinnedRing {
+  static constexpr int kSlots = 4;
+  struct Slot {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaEvent_t ev = nullptr;
+    int dev = -1;
+  } slots[kSlots];
+  int next = 0;
+  ~PinnedRing() {
+    for (Slot& sl : slots) {
+      if (sl.ev) cudaEventDestroy(sl.ev);
+      if (sl.p) cudaFreeHost(sl.p);
+    }
+  }
+  // returns a pinned buffer of at least `bytes`, free for reuse; `after` must be called once the copy is enqueued
+  Slot* acquire(size_t bytes) {
+    Slot& sl = slots[next];
+    next = (next + 1) % kSlots;
+    const int dev = currentDevice();
+    if (sl.ev && sl.dev != dev) { // events belong to a device: start over on a device change
+      cudaEventSynchronize(sl.ev);
+      cudaEventDestroy(sl.ev);
+      sl.ev = nullptr;
+    }
+    if (sl.ev) cudaEventSynchronize(sl.ev);
+    if (sl.cap < bytes) {
+      if (sl.p) cudaFreeHost(sl.p);
+      sl.p = nullptr;
+      sl.cap = 0;
+      const size_t want = roundUpSz(bytes, 4096);
+      if (cudaMallocHost(&sl.p, want) != cudaSuccess) return nullptr;
+      sl.cap = want;
+    }
+    if (!sl.ev) {
+      if (cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+      sl.dev = dev;
+    }
+    return &sl;
+  }
+};
+
 int upload(Temp& tmp, const WorkList& wl, Elem** dev, cudaStream_t s) {
   *dev = tmp.alloc<Elem>(wl.elems.size());
   if (tmp.failed()) return kErrCuda;
-  // pageable source: the runtime stages it before returning, so the vector may die after the call
-  DGB_CUDA(cudaMemcpyAsync(*dev, wl.elems.data(), wl.elems.size() * sizeof(Elem), cudaMemcpyHostToDevice, s));
+  static thread_local PinnedRing ring;
+  const size_t bytes = wl.elems.size() * sizeof(Elem);
+  PinnedRing::Slot* sl = ring.acquire(bytes);
+  if (!sl) return kErrCuda;
+  memcpy(sl->p, wl.elems.data(), bytes);
+  DGB_CUDA(cudaMemcpyAsync(*dev, sl->p, bytes, cudaMemcpyHostToDevice, s));
+  DGB_CUDA(cudaEventRecord(sl->ev, s));
   return kOk;
 }
 
@@ -138,6 +207,7 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
               cudaStream_t s) {
   if (num == 0) return kOk;
   if (!in || !inSize || !out || pb < 9 || pb > 11) return kErrInvalidArg;
+  if (!ansSizesOk(num, inSize)) return kErrInvalidArg;
   for (uint32_t i = 0; i < num; ++i)
     if (((uintptr_t)out[i]) & 15u) return kErrAlignment;
   Temp tmp(temp, tempBytes, s);
@@ -242,15 +312,13 @@ cudaStream_t sideStream() {
 // 0.068 ms fused vs 0.048 ms as separate launches) and, above that, wins when there are elements to overlap
 // (fusedWanted below).
 constexpr uint32_t kFusedMinElems = 1;
-static long long g_fusedMinTiles = -1; // < 0: default (or DGB_FUSED_MIN_TILES); set by dgb_set_fused_min_tiles
+static long long g_fusedMinTiles = -1; // < 0: default (or DGB_FUSED_MIN_TILES); set by dgb_set_fused_min_tiles (atomic accesses)
+static long long fusedMinTilesOverride() { return __atomic_load_n(&g_fusedMinTiles, __ATOMIC_RELAXED); }
 uint32_t fusedMinTiles() {
-  if (g_fusedMinTiles >= 0) return g_fusedMinTiles > 0xffffffffll ? 0xffffffffu : (uint32_t)g_fusedMinTiles;
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("DGB_FUSED_MIN_TILES"); // experiment knob
-    v = e ? atoi(e) : 1024;
-  }
-  return (uint32_t)v;
+  const long long o = fusedMinTilesOverride();
+  if (o >= 0) return o > 0xffffffffll ? 0xffffffffu : (uint32_t)o;
+  const int v = DGB_KNOB("DGB_FUSED_MIN_TILES", -1); // experiment knob
+  return v >= 0 ? (uint32_t)v : 1024u;
 }
 
 // The fused kernel wins by overlapping the split of later elements with the encoding of earlier ones; with few
@@ -261,7 +329,7 @@ uint32_t fusedMinTiles() {
 //   32 x 2 MiB 0.107 / 0.112   2 x 256 MiB 0.483 / 0.530  1 x 1 GiB 0.911 / 0.995    fp32 1 x 1 GiB 0.669 / 0.769
 // An explicit threshold (dgb_set_fused_min_tiles / DGB_FUSED_MIN_TILES) is taken literally.
 bool fusedWanted(uint32_t totalTiles, uint32_t numElems) {
-  if (g_fusedMinTiles >= 0 || getenv("DGB_FUSED_MIN_TILES")) return totalTiles >= fusedMinTiles();
+  if (fusedMinTilesOverride() >= 0 || DGB_KNOB("DGB_FUSED_MIN_TILES", -1) >= 0) return totalTiles >= fusedMinTiles();
   if (totalTiles < 1024) return false;
   if (numElems >= 16) return true;
   if (numElems >= 2 && totalTiles >= 2048) return true;
@@ -269,22 +337,13 @@ bool fusedWanted(uint32_t totalTiles, uint32_t numElems) {
 }
 
 bool fusedCompressEnabled() {
-  static int on = -1;
-  if (on < 0) {
-    const char* e = getenv("DGB_FUSED");
-    on = e ? (atoi(e) != 0) : 1;
-  }
-  return on != 0;
+  return DGB_KNOB("DGB_FUSED", 1) != 0;
 }
 
 int overlapGroups() {
-  static int g = -1;
-  if (g < 0) {
-    const char* e = getenv("DGB_OVERLAP_GROUPS");
-    g = e ? atoi(e) : 1; // measured on B200: 2/4/8 groups are 1-19 % slower than 1 (kernels of two streams do not co-run well)
-    if (g < 1) g = 1;
-    if (g > 16) g = 16;
-  }
+  int g = DGB_KNOB("DGB_OVERLAP_GROUPS", 1); // measured on B200: 2/4/8 groups are 1-19 % slower than 1 (kernels of two streams do not co-run well)
+  if (g < 1) g = 1;
+  if (g > 16) g = 16;
   return g;
 }
 
@@ -385,6 +444,7 @@ int floatCompress(void* temp, size_t tempBytes, int ft, int pb, int useChecksum,
                   cudaStream_t s) {
   if (num == 0) return kOk;
   if (!in || !inSize || !out || !validFloatType(ft) || pb < 9 || pb > 11) return kErrInvalidArg;
+  if (!floatSizesOk(ft, num, inSize)) return kErrInvalidArg;
   const uint32_t wb = floatWordBytes(ft);
   for (uint32_t i = 0; i < num; ++i) {
     if (((uintptr_t)out[i]) & 15u) return kErrAlignment;
@@ -446,6 +506,7 @@ int floatCompressSparse(void* temp, size_t tempBytes, int ft, int pb, int useChe
   if (num == 0) return kOk;
   if (!in || !inSize || !out || !validFloatType(ft) || pb < 9 || pb > 11) return kErrInvalidArg;
   if (useChecksum) return kErrInvalidArg;
+  if (!floatSizesOk(ft, num, inSize, 32)) return kErrInvalidArg;
   const uint32_t wb = floatWordBytes(ft);
   for (uint32_t i = 0; i < num; ++i) {
     if (((uintptr_t)out[i]) & 15u) return kErrAlignment;
@@ -546,6 +607,29 @@ int getInfo(const void* const* in, int inIsDevice, uint32_t num, int floatMode, 
   return kOk;
 }
 
+// ---- size bounds in 64 bits (dietgpu/ans/GpuANSEncode.cu:13-25, dietgpu/float/GpuFloatCompress.cu:23-47) --------
+uint64_t ansMaxBytes64(uint64_t n) {
+  const uint64_t blocks = (n + kBlockSyms - 1) / kBlockSyms;
+  uint64_t raw = ansOverhead(kBlockSyms);
+  raw += (uint64_t)roundUp(kBlockSyms + kBlockSyms / 4, 16) * blocks;
+  return roundUpSz(raw, 16);
+}
+uint64_t floatRawBytes64(int ft, uint64_t n) {
+  switch (ft) {
+    case kFtF16:
+    case kFtBF16: return roundUpSz(n, 16);
+    case kFtF32: return 2 * roundUpSz(n, 8) + roundUpSz(n, 16);
+    case kFtF64: return 4 * roundUpSz(n, 4) + 2 * roundUpSz(n, 8);
+    default: return 0;
+  }
+}
+// > UINT32_MAX also when the ANS part alone would have made the reference abort
+uint64_t floatMaxBytes64(int ft, uint64_t n) {
+  const uint64_t a = ansMaxBytes64(n);
+  if (a > 0x7fffffffull) return ~0ull;
+  return kFloatHeaderBytes + a + floatRawBytes64(ft, n) + (ft == kFtF64 ? a : 0);
+}
+
 // ---- stride / split-size addressing -> pointer arrays -------------------------------------------
 struct PtrArrays {
   std::vector<const void*> in;
@@ -564,26 +648,28 @@ const char* dgb_version(void) { return "dietgpu_b200 r1 sm_100a"; }
 
 size_t dgb_last_temp_bytes_used(void) { return Temp::lastHighWater(); }
 
-void dgb_set_fused_min_tiles(long long tiles) { g_fusedMinTiles = tiles; }
+void dgb_set_fused_min_tiles(long long tiles) { __atomic_store_n(&g_fusedMinTiles, tiles, __ATOMIC_RELAXED); }
 
 // dietgpu/ans/GpuANSEncode.cu:13-25: the reference passes the block SIZE (4096) where
 // getCompressedOverhead expects a block COUNT; the value is part of the API (Python sizes and
 // validates buffers with it), so it is reproduced.
+// All three bounds are computed in 64 bits and return 0 ("no valid bound") when the result leaves the range the
+// 32-bit API can express: the reference CHECK-aborts when the ANS bound exceeds INT32_MAX (same file, :22) and lets
+// the uint32 float sums wrap silently; callers here must treat 0 for n > 0 as an error (codec.py / torch_ops.py raise).
 uint32_t dgb_ans_max_compressed_size(uint32_t n) {
-  uint32_t blocks = divUp(n, kBlockSyms);
-  size_t raw = ansOverhead(kBlockSyms);
-  raw += (size_t)roundUp(kBlockSyms + kBlockSyms / 4, 16) * blocks;
-  return (uint32_t)roundUpSz(raw, 16);
+  const uint64_t v = ansMaxBytes64(n);
+  return v > 0x7fffffffull ? 0u : (uint32_t)v;
 }
 
 uint32_t dgb_float_max_compressed_size(int ft, uint32_t n) {
-  uint32_t base = kFloatHeaderBytes + dgb_ans_max_compressed_size(n) + floatRawBytes(ft, n);
-  if (ft == kFtF64) base += dgb_ans_max_compressed_size(n);
-  return base;
+  const uint64_t v = floatMaxBytes64(ft, n);
+  return v > 0xffffffffull ? 0u : (uint32_t)v;
 }
 
 uint32_t dgb_sparse_float_max_compressed_size(int ft, uint32_t n) {
-  return 16u + sparseBitmapBytes(n) + dgb_float_max_compressed_size(ft, n);
+  const uint64_t f = floatMaxBytes64(ft, n);
+  const uint64_t v = f + 16u + roundUpSz(((uint64_t)n + 7) / 8, 16);
+  return (f > 0xffffffffull || v > 0xffffffffull) ? 0u : (uint32_t)v;
 }
 
 size_t dgb_temp_bytes_required(int op, int ft, uint32_t num, uint32_t maxSize) {

@@ -33,7 +33,7 @@ constexpr uint32_t kStageWords = 88 * 32;                // 2816 u16 = 5632 B pe
 
 enum FloatType : int { kFtNone = 0, kFtF16 = 1, kFtBF16 = 2, kFtF32 = 3, kFtF64 = 4 };
 
-__host__ __device__ __forceinline__ uint32_t divUp(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+__host__ __device__ __forceinline__ uint32_t divUp(uint32_t a, uint32_t b) { return a / b + (a % b != 0); } // no wrap near 2^32
 __host__ __device__ __forceinline__ uint32_t roundUp(uint32_t a, uint32_t b) { return divUp(a, b) * b; }
 __host__ __device__ __forceinline__ size_t roundUpSz(size_t a, size_t b) { return (a + b - 1) / b * b; }
 

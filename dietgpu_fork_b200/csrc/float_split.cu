@@ -82,12 +82,19 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
 template <int FT>
 static int launchSplitT(SplitParams& p, cudaStream_t s) {
   constexpr uint32_t smemBytes = FloatTraits<FT>::kPlanes * splitHistWords<256>() * 4;
-  static const bool pipe = getenv("DGB_SPLIT_PIPE") ? atoi(getenv("DGB_SPLIT_PIPE")) != 0 : true; // experiment knob
+  const bool pipe = DGB_KNOB("DGB_SPLIT_PIPE", 1) != 0; // experiment knob
   auto kern = pipe ? k_floatSplit<FT, true> : k_floatSplit<FT, false>;
-  DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  {
+    static DeviceOnce once[2];
+    const int dev = currentDevice();
+    if (once[pipe].first(dev)) {
+      DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+      once[pipe].done(dev);
+    }
+  }
   const uint32_t tiles = p.tileEnd - p.tileBegin;
   uint32_t perSm = FT == kFtF64 ? 3u : 6u;
-  if (const char* e = getenv("DGB_SPLIT_CTAS")) perSm = (uint32_t)atoi(e); // experiment knob
+  if (DGB_KNOB("DGB_SPLIT_CTAS", 0) > 0) perSm = (uint32_t)DGB_KNOB("DGB_SPLIT_CTAS", 0); // experiment knob
   uint32_t ctas = min(tiles, (uint32_t)smCount() * perSm);
   p.tilesPerCta = divUp(tiles, ctas);
   ctas = divUp(tiles, p.tilesPerCta);
@@ -99,20 +106,20 @@ static int launchSplitT(SplitParams& p, cudaStream_t s) {
     // ranges 123.7 us, round robin in units of 32768 / 16384 / 8192 / 4096 words 108.5 / 104.3 / 110.7 / 121.1 us
     const uint32_t full = (uint32_t)smCount() * perSm;
     bool rr = (uint64_t)tiles >= (uint64_t)full * p.numElems;
-    if (const char* e = getenv("DGB_SPLIT_RR")) rr = atoi(e) != 0; // experiment knob
+    if (DGB_KNOB("DGB_SPLIT_RR", kKnobUnset) != kKnobUnset) rr = DGB_KNOB("DGB_SPLIT_RR", kKnobUnset) != 0; // experiment knob
     if (rr) {
       p.unitShift = 1;
-      if (const char* e = getenv("DGB_SPLIT_RR_SHIFT")) p.unitShift = (uint32_t)atoi(e);
+      if (DGB_KNOB("DGB_SPLIT_RR_SHIFT", -1) >= 0) p.unitShift = (uint32_t)DGB_KNOB("DGB_SPLIT_RR_SHIFT", -1);
       p.roundRobin = 1;
       ctas = min(tiles << p.unitShift, full);
     } else {
       // several elements, each long enough to get CTAs of its own: round robin inside every element
       bool per = p.tileBegin == 0 && p.minElemTiles >= 2 * divUp(tiles, min(tiles, full)) && tiles >= full;
-      if (const char* e = getenv("DGB_SPLIT_RR_ELEM")) per = per && atoi(e) != 0; // experiment knob
+      per = per && DGB_KNOB("DGB_SPLIT_RR_ELEM", 1) != 0; // experiment knob
       if (per) {
         p.unitShift = 1; // at least four units per CTA, so that the CTAs of an element finish together
         while (p.unitShift < 3 && ((uint64_t)tiles << p.unitShift) < 4ull * full) ++p.unitShift;
-        if (const char* e = getenv("DGB_SPLIT_RR_SHIFT")) p.unitShift = (uint32_t)atoi(e);
+        if (DGB_KNOB("DGB_SPLIT_RR_SHIFT", -1) >= 0) p.unitShift = (uint32_t)DGB_KNOB("DGB_SPLIT_RR_SHIFT", -1);
         p.roundRobin = 2;
         ctas = full;
       }

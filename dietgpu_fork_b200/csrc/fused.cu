@@ -283,13 +283,23 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
 template <int FT, int PB>
 static int launchFusedT(FusedParams& p, cudaStream_t s) {
   auto kern = k_compressFused<FT, PB>;
-  DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmem));
-  int perSm = 0;
-  DGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, (int)kFusedThreads, kFusedSmem));
+  // attribute + occupancy query once per (kernel, device)
+  static DeviceOnce once;
+  static int perSmByDev[kMaxDevices] = {};
+  const int dev = currentDevice();
+  if (once.first(dev)) {
+    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmem));
+    int q = 0;
+    DGB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, (int)kFusedThreads, kFusedSmem));
+    __atomic_store_n(&perSmByDev[dev], q, __ATOMIC_RELAXED);
+    once.done(dev);
+  }
+  int perSm = __atomic_load_n(&perSmByDev[dev], __ATOMIC_RELAXED);
   if (perSm < 2) return kErrInternal;
   if (perSm > (int)kEncCtasPerSm) perSm = (int)kEncCtasPerSm;
   uint32_t splitPerSm = 3; // measured on B200 (bf16, 128 x 4 MiB): 2: 0.507, 3: 0.424, 4: 0.442, 5: 0.443 ms
-  if (const char* e = getenv("DGB_FUSED_SPLIT_CTAS")) splitPerSm = (uint32_t)atoi(e); // experiment knob
+  const int knobSplitCtas = DGB_KNOB("DGB_FUSED_SPLIT_CTAS", 0); // experiment knob
+  if (knobSplitCtas > 0) splitPerSm = (uint32_t)knobSplitCtas;
   if (splitPerSm < 1) splitPerSm = 1;
   if (splitPerSm >= (uint32_t)perSm) splitPerSm = (uint32_t)perSm - 1;
   // (few elements: making every CTA split first was measured slower - fp32 1 x 1 GiB 0.81 ms vs 0.72 ms)
@@ -303,7 +313,7 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   p.compactBetweenRuns = 0;
   {
     const uint64_t splitCtas = (uint64_t)splitPerSm * (uint64_t)smCount();
-    if (const char* e = getenv("DGB_SPLIT_FINE_TILES")) p.fineSlices = (uint32_t)atoi(e) << p.sliceShift; // experiment knob
+    if (DGB_KNOB("DGB_SPLIT_FINE_TILES", 0) > 0) p.fineSlices = (uint32_t)DGB_KNOB("DGB_SPLIT_FINE_TILES", 0) << p.sliceShift; // experiment knob
     if ((uint64_t)p.totalTiles >= splitCtas * (uint64_t)p.sp.numElems) {
       p.fineSlices = 0xfffffff0u; // everything
       // and compaction is interleaved with the runs (fp32 1 x 1 GiB: 0.682 -> 0.669 ms; for batches of many
@@ -313,16 +323,16 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
       // nothing can be encoded before the first table exists and there are few tables to wait for: all CTAs
       // but one per SM split (fp32 1 x 1 GiB on B200: 0.73 ms with 3 split CTAs per SM and whole tiles,
       // 0.69 ms with 9 and slices; 9 with whole tiles thrash DRAM: 0.81 ms)
-      if (!getenv("DGB_FUSED_SPLIT_CTAS")) p.splitCtasPerSm = (uint32_t)perSm - 1;
+      if (knobSplitCtas <= 0) p.splitCtasPerSm = (uint32_t)perSm - 1;
     }
     {
       uint32_t rounds = 2, tail = 8; // B200: single tiles over the last two rounds: fp32 64 x 16 MiB 0.557 -> 0.542 ms, bf16 equal; 2- and 4-slice claims are slower
-      if (const char* e = getenv("DGB_SPLIT_TAIL_ROUNDS")) rounds = (uint32_t)atoi(e); // experiment knobs
-      if (const char* e = getenv("DGB_SPLIT_TAIL_CLAIM")) tail = (uint32_t)max(1, atoi(e));
+      if (DGB_KNOB("DGB_SPLIT_TAIL_ROUNDS", -1) >= 0) rounds = (uint32_t)DGB_KNOB("DGB_SPLIT_TAIL_ROUNDS", -1); // experiment knobs
+      if (DGB_KNOB("DGB_SPLIT_TAIL_CLAIM", 0) > 0) tail = (uint32_t)DGB_KNOB("DGB_SPLIT_TAIL_CLAIM", 0);
       p.tailSlices = rounds * (uint32_t)splitCtas * p.splitClaim;
       p.tailClaim = tail;
     }
-    if (const char* e = getenv("DGB_COMPACT_BETWEEN_RUNS")) p.compactBetweenRuns = atoi(e) != 0; // experiment knob
+    if (DGB_KNOB("DGB_COMPACT_BETWEEN_RUNS", -1) >= 0) p.compactBetweenRuns = DGB_KNOB("DGB_COMPACT_BETWEEN_RUNS", -1) != 0; // experiment knob
     if (!p.coalClaim) p.compactBetweenRuns = 0;
     if (p.fineSlices > (p.totalTiles << p.sliceShift)) p.fineSlices = p.totalTiles << p.sliceShift;
     p.fineSlices = p.fineSlices / p.splitClaim * p.splitClaim;
@@ -397,7 +407,7 @@ int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, ui
   p.ready = p.tilesDone + a.numElems;
   p.runsDone = p.ready + a.numElems;
   p.ep.tileWords = p.runsDone + a.numElems;
-  static const bool separateCoalesce = getenv("DGB_FUSED_COALESCE") && atoi(getenv("DGB_FUSED_COALESCE")) == 0;
+  const bool separateCoalesce = DGB_KNOB("DGB_FUSED_COALESCE", 1) == 0;
   p.coalClaim = separateCoalesce ? nullptr : es.fusedCtrl + kFusedCtrlCoal; // experiment knob
   p.ep.ready = p.ready;
   p.totalTiles = totalTiles;

@@ -23,29 +23,22 @@
 
 #include "../../include/dietgpu_b200.h"
 #include "internal.h"
+#include "knobs.h"
 
 namespace dgb {
 namespace {
 
 constexpr int kPipeLanes = 4; // lanes that exist; lanesInUse() of them take groups
 int lanesInUse() { // DGB_HOST_LANES is an experiment knob
-  static int v = 0;
-  if (!v) {
-    const char* e = getenv("DGB_HOST_LANES");
-    v = e ? atoi(e) : 3;
-    if (v < 2) v = 2;
-    if (v > kPipeLanes) v = kPipeLanes;
-  }
+  int v = DGB_KNOB("DGB_HOST_LANES", 3);
+  if (v < 2) v = 2;
+  if (v > kPipeLanes) v = kPipeLanes;
   return v;
 }
 // input bytes per group (at least one element); DGB_HOST_GROUP_MB is an experiment knob
 size_t groupBytes() {
-  static size_t v = 0;
-  if (!v) {
-    const char* e = getenv("DGB_HOST_GROUP_MB");
-    v = (size_t)(e && atoi(e) > 0 ? atoi(e) : 16) << 20;
-  }
-  return v;
+  const int mb = DGB_KNOB("DGB_HOST_GROUP_MB", 16);
+  return (size_t)(mb > 0 ? mb : 16) << 20;
 }
 
 struct Lane {

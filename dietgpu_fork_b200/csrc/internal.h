@@ -42,7 +42,7 @@ struct DecInfo {
   uint32_t nb;          // blocks
   uint32_t n;         // symbols
   uint32_t ok;        // capacity >= n and header sane
-  uint32_t pad;
+  uint32_t totalWords; // payload length in 16-bit words (header): bounds the block index entries
 };
 
 // Bump allocator over the caller's temp buffer; anything that does not fit is taken from the
@@ -112,7 +112,24 @@ class Temp {
     }                                                                                    \
   } while (0)
 
+// current device, clamped to [0, kMaxDevices)
+constexpr int kMaxDevices = 64;
+int currentDevice();
+// SM count of the current device (cached per device)
 int smCount();
+
+// "do this once per device" guard for per-kernel attribute calls (one static instance per call site)
+struct DeviceOnce {
+  unsigned long long mask = 0;
+  // true exactly for the first caller per device (benign race: a second thread may repeat the idempotent call)
+  bool first(int dev) {
+    const unsigned long long bit = 1ull << (dev & 63);
+    const unsigned long long seen = __atomic_load_n(&mask, __ATOMIC_ACQUIRE);
+    if (seen & bit) return false;
+    return true;
+  }
+  void done(int dev) { __atomic_fetch_or(&mask, 1ull << (dev & 63), __ATOMIC_RELEASE); }
+};
 
 // ---- launchers implemented in ans.cu ------------------------------------------------------
 struct EncodeArgs {

@@ -12,6 +12,7 @@
 #include <cstdlib>
 
 #include "internal.h"
+#include "knobs.h"
 #include "prof.h"
 
 namespace dgb {
@@ -250,7 +251,7 @@ int launchSparseCompact(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
   if (tmp.failed()) return kErrCuda;
   p.dense = dense;
   p.nnz = nnz;
-  p.prefetch = getenv("DGB_SPARSE_PREFETCH") ? atoi(getenv("DGB_SPARSE_PREFETCH")) : 1; // experiment knob
+  p.prefetch = DGB_KNOB("DGB_SPARSE_PREFETCH", 1); // experiment knob
   DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
   uint32_t grid = min(totalTiles, (uint32_t)smCount() * 4u);
   ProfScope ps__("k_sparseCompact", s);
@@ -275,7 +276,7 @@ int launchSparseScatter(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
   p.outSize = outSize;
   DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
   uint32_t perSm = 8; // 32 registers: all 64 warps of an SM
-  if (const char* e = getenv("DGB_SPARSE_SCATTER_CTAS")) perSm = (uint32_t)max(1, atoi(e)); // experiment knob
+  if (DGB_KNOB("DGB_SPARSE_SCATTER_CTAS", 0) > 0) perSm = (uint32_t)DGB_KNOB("DGB_SPARSE_SCATTER_CTAS", 0); // experiment knob
   uint32_t grid = min(totalTiles, (uint32_t)smCount() * perSm);
   ProfScope ps__("k_sparseScatter", s);
   switch (floatWordBytes(ft)) {

@@ -105,4 +105,45 @@ int ref_float_decompress_sparse(void* temp, size_t tempBytes, int floatType, int
   return (int)st.error;
 }
 
+/* ansEncodeBatchStride / ansDecodeBatchStride, dietgpu/ans/GpuANSCodec.h:68-98, :222-257 */
+void ref_ans_encode_batch_stride(void* temp, size_t tempBytes, int probBits, int useChecksum,
+                                 uint32_t numInBatch, const void* in_dev, uint32_t inPerBatchSize,
+                                 uint32_t inPerBatchStride, const uint32_t* histogram_dev,
+                                 void* out_dev, uint32_t outPerBatchStride, uint32_t* outSize_dev,
+                                 cudaStream_t stream) {
+  StackDeviceMemory res(curDev(), temp, tempBytes);
+  ansEncodeBatchStride(res, ANSCodecConfig(probBits, useChecksum != 0), numInBatch, in_dev,
+                       inPerBatchSize, inPerBatchStride, histogram_dev, out_dev, outPerBatchStride,
+                       outSize_dev, stream);
+}
+
+int ref_ans_decode_batch_stride(void* temp, size_t tempBytes, int probBits, int useChecksum,
+                                uint32_t numInBatch, const void* in_dev, uint32_t inPerBatchStride,
+                                void* out_dev, uint32_t outPerBatchStride,
+                                uint32_t outPerBatchCapacity, uint8_t* outSuccess_dev,
+                                uint32_t* outSize_dev, cudaStream_t stream) {
+  StackDeviceMemory res(curDev(), temp, tempBytes);
+  auto st = ansDecodeBatchStride(res, ANSCodecConfig(probBits, useChecksum != 0), numInBatch,
+                                 in_dev, inPerBatchStride, out_dev, outPerBatchStride,
+                                 outPerBatchCapacity, outSuccess_dev, outSize_dev, stream);
+  return (int)st.error;
+}
+
+/* ansGetCompressedInfo, dietgpu/ans/GpuANSCodec.h:315-328 */
+void ref_ans_get_compressed_info(void* temp, size_t tempBytes, const void** in,
+                                 uint32_t numInBatch, uint32_t* outSizes_dev,
+                                 uint32_t* outChecksum_dev, cudaStream_t stream) {
+  StackDeviceMemory res(curDev(), temp, tempBytes);
+  ansGetCompressedInfo(res, in, numInBatch, outSizes_dev, outChecksum_dev, stream);
+}
+
+/* floatGetCompressedInfo, dietgpu/float/GpuFloatCodec.h:281-300 */
+void ref_float_get_compressed_info(void* temp, size_t tempBytes, const void** in,
+                                   uint32_t numInBatch, uint32_t* outSizes_dev,
+                                   uint32_t* outTypes_dev, uint32_t* outChecksum_dev,
+                                   cudaStream_t stream) {
+  StackDeviceMemory res(curDev(), temp, tempBytes);
+  floatGetCompressedInfo(res, in, numInBatch, outSizes_dev, outTypes_dev, outChecksum_dev, stream);
+}
+
 } // extern "C"

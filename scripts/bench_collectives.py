@@ -32,55 +32,43 @@ def timed(fn, steps, warmup):
     return ms.item()
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--mib", type=int, default=64)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--chunks", type=int, default=4)
-    ap.add_argument("--peer", type=int, default=1, help="also time the peer-memory collectives (CUDA IPC)")
-    a = ap.parse_args()
-    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
-    dist.init_process_group("nccl")
-    n = a.mib * (1 << 20) // 2
+def measure(dist_mod, rank, world, mib=64, steps=10, warmup=3, chunks=1, peer=True):
+    """Runs inside an initialised NCCL process group (one rank per GPU, device already selected). Returns a dict:
+    raw NCCL, archives moved by NCCL, and the peer-memory form, for all-gather and all-to-all; every compressed
+    result is compared bit for bit with the uncompressed collective's before and after timing."""
+    n = mib * (1 << 20) // 2
     g = torch.Generator(device="cuda").manual_seed(5000 + rank)
     shard = (torch.randn(n, device="cuda", generator=g) * 0.02).to(torch.bfloat16)
     temp = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     codec = dgd.CudaFloatCodec(temp_mem=temp)
+    res = {"workload": f"bf16 N(0, 0.02), {mib} MiB per rank, {world} GPUs", "n_gpus": world, "shard_mib": mib,
+           "chunks": chunks, "unit": "GB/s of uncompressed bytes delivered per rank", "bit_exact": True}
 
     # --- all-gather ---
     raw = torch.empty((world, n), dtype=torch.bfloat16, device="cuda")
     out = torch.empty_like(raw)
     dist.all_gather_into_tensor(raw.view(-1), shard)
-    dgd.all_gather_compressed(shard, out=out, num_chunks=a.chunks, codec=codec)
+    dgd.all_gather_compressed(shard, out=out, num_chunks=chunks, codec=codec)
     assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "compressed all-gather is not bit exact"
-    t_raw = timed(lambda: dist.all_gather_into_tensor(raw.view(-1), shard), a.steps, a.warmup)
-    t_cmp = timed(lambda: dgd.all_gather_compressed(shard, out=out, num_chunks=a.chunks, codec=codec), a.steps,
-                  a.warmup)
+    t_raw = timed(lambda: dist.all_gather_into_tensor(raw.view(-1), shard), steps, warmup)
+    t_cmp = timed(lambda: dgd.all_gather_compressed(shard, out=out, num_chunks=chunks, codec=codec), steps, warmup)
     delivered = world * n * 2
-    res = {"collective": "all_gather", "n_gpus": world, "shard_mib": a.mib, "chunks": a.chunks,
-           "nccl_raw_ms": t_raw, "compressed_ms": t_cmp,
-           "nccl_raw_gbs": delivered / t_raw / 1e6, "compressed_effective_gbs": delivered / t_cmp / 1e6}
-    if rank == 0:
-        print(json.dumps(res), flush=True)
-
-    # --- all-gather through peer memory (exchange fused into the decompress kernel) ---
+    ag = {"nccl_raw_ms": round(t_raw, 4), "nccl_raw": round(delivered / t_raw / 1e6, 1),
+          "compressed_nccl_ms": round(t_cmp, 4), "compressed_nccl": round(delivered / t_cmp / 1e6, 1)}
     peers = None
-    if a.peer:
-        peers = dgd.PeerBuffers(max(dgd.peer_bytes_needed(torch.bfloat16, n, a.chunks),
+    if peer:
+        peers = dgd.PeerBuffers(max(dgd.peer_bytes_needed(torch.bfloat16, n, chunks),
                                     dgd.peer_bytes_needed(torch.bfloat16, n // world, 1) * world))
         out.zero_()
-        dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=a.chunks, temp=temp)
+        dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=chunks, temp=temp)
         torch.cuda.synchronize()
         assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather is not bit exact"
-        t_peer = timed(lambda: dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=a.chunks, temp=temp),
-                       a.steps, a.warmup)
+        t_peer = timed(lambda: dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=chunks, temp=temp),
+                       steps, warmup)
         assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather is not bit exact (timed)"
-        if rank == 0:
-            print(json.dumps({"collective": "all_gather_peer", "n_gpus": world, "shard_mib": a.mib, "chunks": a.chunks,
-                              "nccl_raw_ms": t_raw, "peer_ms": t_peer, "nccl_raw_gbs": delivered / t_raw / 1e6,
-                              "peer_effective_gbs": delivered / t_peer / 1e6}), flush=True)
+        ag.update({"compressed_peer_ms": round(t_peer, 4), "compressed_peer": round(delivered / t_peer / 1e6, 1),
+                   "peer_vs_raw": round(t_raw / t_peer, 3)})
+    res["all_gather"] = ag
 
     # --- all-to-all: mib/world MiB to every peer ---
     per = n // world
@@ -90,26 +78,40 @@ def main():
     dist.all_to_all_single(raw2.view(-1), send.reshape(-1))
     dgd.all_to_all_compressed(send, out=out2, codec=codec)
     assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "compressed all-to-all is not bit exact"
-    t_raw = timed(lambda: dist.all_to_all_single(raw2.view(-1), send.reshape(-1)), a.steps, a.warmup)
-    t_cmp = timed(lambda: dgd.all_to_all_compressed(send, out=out2, codec=codec), a.steps, a.warmup)
+    t_raw = timed(lambda: dist.all_to_all_single(raw2.view(-1), send.reshape(-1)), steps, warmup)
+    t_cmp = timed(lambda: dgd.all_to_all_compressed(send, out=out2, codec=codec), steps, warmup)
     delivered = world * per * 2
-    res = {"collective": "all_to_all", "n_gpus": world, "chunk_mib": per * 2 / (1 << 20),
-           "nccl_raw_ms": t_raw, "compressed_ms": t_cmp,
-           "nccl_raw_gbs": delivered / t_raw / 1e6, "compressed_effective_gbs": delivered / t_cmp / 1e6}
-    if rank == 0:
-        print(json.dumps(res), flush=True)
+    aa = {"chunk_mib": per * 2 / (1 << 20), "nccl_raw_ms": round(t_raw, 4),
+          "nccl_raw": round(delivered / t_raw / 1e6, 1), "compressed_nccl_ms": round(t_cmp, 4),
+          "compressed_nccl": round(delivered / t_cmp / 1e6, 1)}
     if peers is not None:
         out2.zero_()
         dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp)
         torch.cuda.synchronize()
         assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "peer all-to-all is not bit exact"
-        t_peer = timed(lambda: dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp), a.steps, a.warmup)
+        t_peer = timed(lambda: dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp), steps, warmup)
         assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "peer all-to-all is not bit exact (timed)"
-        if rank == 0:
-            print(json.dumps({"collective": "all_to_all_peer", "n_gpus": world, "chunk_mib": per * 2 / (1 << 20),
-                              "nccl_raw_ms": t_raw, "peer_ms": t_peer, "nccl_raw_gbs": delivered / t_raw / 1e6,
-                              "peer_effective_gbs": delivered / t_peer / 1e6}), flush=True)
+        aa.update({"compressed_peer_ms": round(t_peer, 4), "compressed_peer": round(delivered / t_peer / 1e6, 1),
+                   "peer_vs_raw": round(t_raw / t_peer, 3)})
         peers.close()
+    res["all_to_all"] = aa
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mib", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--chunks", type=int, default=1)
+    ap.add_argument("--peer", type=int, default=1, help="also time the peer-memory collectives (CUDA IPC)")
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    res = measure(dist, rank, world, a.mib, a.steps, a.warmup, a.chunks, bool(a.peer))
+    if rank == 0:
+        print(json.dumps(res), flush=True)
     dist.destroy_process_group()
 
 

@@ -24,6 +24,11 @@ def ref_lib():
             return None
         L = C.CDLL(REF_PATH)
         L.ref_ans_max_compressed_size.restype = C.c_uint32
+        L.ref_ans_max_compressed_size.argtypes = [C.c_uint32]
+        L.ref_float_max_compressed_size.restype = C.c_uint32
+        L.ref_float_max_compressed_size.argtypes = [C.c_int, C.c_uint32]
+        L.ref_sparse_float_max_compressed_size.restype = C.c_uint32
+        L.ref_sparse_float_max_compressed_size.argtypes = [C.c_int, C.c_uint32]
         _ref = L
     return _ref
 
@@ -68,12 +73,13 @@ def alloc_outs(n, row_bytes, fill=0):
 
 
 # ---------------------------------------------------------------- ours
-def ours_ans_encode(dev_ins, pb=10, checksum=False, temp=None, fill=0):
+def ours_ans_encode(dev_ins, pb=10, checksum=False, temp=None, fill=0, histogram=None):
     n = len(dev_ins)
     mx = max([codec.get_max_compressed_size(t.numel()) for t in dev_ins])
     m = alloc_outs(n, mx, fill)
     sizes = torch.zeros(n, dtype=torch.int32, device="cuda")
-    codec.ans_encode_batch_pointer(dev_ins, [m[i] for i in range(n)], sizes, pb, checksum, temp=temp)
+    codec.ans_encode_batch_pointer(dev_ins, [m[i] for i in range(n)], sizes, pb, checksum, histogram=histogram,
+                                   temp=temp)
     torch.cuda.synchronize()
     sz = sizes.cpu().numpy().astype(np.int64)
     return m, sz
@@ -119,7 +125,7 @@ def ours_float_decompress(ft, archives, caps, pb=10, checksum=False, sparse=Fals
 
 
 # ---------------------------------------------------------------- reference CUDA build
-def ref_ans_encode(dev_ins, pb=10, checksum=False, fill=0xCD):
+def ref_ans_encode(dev_ins, pb=10, checksum=False, fill=0xCD, histogram=None):
     L = ref_lib()
     n = len(dev_ins)
     mx = max([codec.get_max_compressed_size(t.numel()) for t in dev_ins])
@@ -127,7 +133,8 @@ def ref_ans_encode(dev_ins, pb=10, checksum=False, fill=0xCD):
     sizes = torch.zeros(n, dtype=torch.int32, device="cuda")
     t = ref_temp()
     L.ref_ans_encode_batch_pointer(C.c_void_p(t.data_ptr()), C.c_size_t(t.numel()), pb, int(checksum), n,
-                                   _ptr_array(dev_ins), _u32([x.numel() for x in dev_ins]), None,
+                                   _ptr_array(dev_ins), _u32([x.numel() for x in dev_ins]),
+                                   None if histogram is None else C.c_void_p(histogram.data_ptr()),
                                    _ptr_array([m[i] for i in range(n)]), C.c_void_p(sizes.data_ptr()),
                                    _stream())
     torch.cuda.synchronize()
@@ -181,3 +188,63 @@ def ref_float_decompress(ft, archives, caps, pb=10, checksum=False, sparse=False
 
 def row_bytes(m, i, size):
     return m[i, :size].cpu().numpy()
+
+
+# ---------------------------------------------------------------- stride addressing / info (both libraries)
+def ref_ans_encode_stride(in_dev, num, in_size, in_stride, out_dev, out_stride, sizes, pb=10, checksum=False):
+    L = ref_lib()
+    t = ref_temp()
+    L.ref_ans_encode_batch_stride(C.c_void_p(t.data_ptr()), C.c_size_t(t.numel()), pb, int(checksum), num,
+                                  C.c_void_p(in_dev.data_ptr()), C.c_uint32(in_size), C.c_uint32(in_stride), None,
+                                  C.c_void_p(out_dev.data_ptr()), C.c_uint32(out_stride),
+                                  C.c_void_p(sizes.data_ptr()), _stream())
+    torch.cuda.synchronize()
+
+
+def ref_ans_decode_stride(in_dev, num, in_stride, out_dev, out_stride, cap, ok, sizes, pb=10, checksum=False):
+    L = ref_lib()
+    t = ref_temp()
+    rc = L.ref_ans_decode_batch_stride(C.c_void_p(t.data_ptr()), C.c_size_t(t.numel()), pb, int(checksum), num,
+                                       C.c_void_p(in_dev.data_ptr()), C.c_uint32(in_stride),
+                                       C.c_void_p(out_dev.data_ptr()), C.c_uint32(out_stride), C.c_uint32(cap),
+                                       C.c_void_p(ok.data_ptr()), C.c_void_p(sizes.data_ptr()), _stream())
+    torch.cuda.synchronize()
+    return rc
+
+
+def ref_ans_info(archives):
+    L = ref_lib()
+    n = len(archives)
+    t = ref_temp()
+    sizes = torch.zeros(n, dtype=torch.int32, device="cuda")
+    cks = torch.zeros(n, dtype=torch.int32, device="cuda")
+    L.ref_ans_get_compressed_info(C.c_void_p(t.data_ptr()), C.c_size_t(t.numel()), _ptr_array(archives), n,
+                                  C.c_void_p(sizes.data_ptr()), C.c_void_p(cks.data_ptr()), _stream())
+    torch.cuda.synchronize()
+    return sizes.cpu().numpy(), cks.cpu().numpy()
+
+
+def ref_float_info(archives):
+    L = ref_lib()
+    n = len(archives)
+    t = ref_temp()
+    sizes = torch.zeros(n, dtype=torch.int32, device="cuda")
+    types = torch.zeros(n, dtype=torch.int32, device="cuda")
+    cks = torch.zeros(n, dtype=torch.int32, device="cuda")
+    L.ref_float_get_compressed_info(C.c_void_p(t.data_ptr()), C.c_size_t(t.numel()), _ptr_array(archives), n,
+                                    C.c_void_p(sizes.data_ptr()), C.c_void_p(types.data_ptr()),
+                                    C.c_void_p(cks.data_ptr()), _stream())
+    torch.cuda.synchronize()
+    return sizes.cpu().numpy(), types.cpu().numpy(), cks.cpu().numpy()
+
+
+def assert_rows_match_ref(m, sz, rm, rsz, mask_fn, what):
+    """Every archive of `m` equals the reference build's under the defined-byte mask (bytes the reference never
+    writes are 0 in ours and whatever the fill was in its buffer)."""
+    assert list(sz) == list(rsz), f"{what}: compressed sizes differ from the reference build"
+    for i in range(len(sz)):
+        a, r = row_bytes(m, i, sz[i]), row_bytes(rm, i, sz[i])
+        mask = mask_fn(a)
+        bad = np.nonzero((a != r) & mask)[0]
+        assert bad.size == 0, f"{what}: archive {i} differs from the reference build at {bad[:8]} ({bad.size} bytes)"
+        assert not a[~mask].any(), f"{what}: archive {i} has non-zero bytes where the format defines none"
