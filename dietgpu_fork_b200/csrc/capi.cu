@@ -106,12 +106,8 @@ struct PinnedRing {
     int dev = -1;
   } slots[kSlots];
   int next = 0;
-  ~PinnedRing() {
-    for (Slot& sl : slots) {
-      if (sl.ev) cudaEventDestroy(sl.ev);
-      if (sl.p) cudaFreeHost(sl.p);
-    }
-  }
+  // no destructor on purpose: a thread-local destructor may run while the CUDA runtime is being torn down at process
+  // exit; the few KB of pinned memory per calling thread are reclaimed with the context
   // returns a pinned buffer of at least `bytes`, free for reuse; `after` must be called once the copy is enqueued
   Slot* acquire(size_t bytes) {
     Slot& sl = slots[next];

@@ -166,7 +166,12 @@ class PeerBuffers:
     """One archive buffer per rank, mapped by every rank of the group (all on one node). Two halves are used in
     turn by successive collectives, which is what lets one barrier per call suffice: a rank reaches the barrier
     of call k + 1 only after its own decode of call k, so when any rank passes that barrier and later overwrites
-    half (k + 2) % 2 == k % 2, nobody is still reading it."""
+    half (k + 2) % 2 == k % 2, nobody is still reading it.
+
+    Like any collective, this requires every rank of the group to issue the SAME sequence of peer collectives on one
+    PeerBuffers object (all-gather and all-to-all calls in the same order, on the same stream): the half a call uses
+    is chosen by a local call counter, not negotiated. tests/multigpu_worker.py runs five consecutive mixed calls
+    with one rank artificially delayed to exercise the reuse."""
 
     def __init__(self, half_bytes, group=None, device=None):
         import ctypes as C

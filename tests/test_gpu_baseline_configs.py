@@ -307,12 +307,15 @@ def test_max_compressed_sizes_match_reference_build():
           (256 << 20) + 3, 1 << 30]
     rng = np.random.default_rng(4)
     ns += [int(x) for x in rng.integers(1, 1 << 30, 64)]
+    lib = _capi.lib  # the raw C ABI: 0 = "no bound the 32-bit API can express" (codec.py raises on it)
     for n in ns:
-        assert codec.get_max_compressed_size(n) == L.ref_ans_max_compressed_size(n), f"ANS bound at {n}"
+        assert lib.dgb_ans_max_compressed_size(n) == L.ref_ans_max_compressed_size(n), f"ANS bound at {n}"
         for ft in (F16, BF16, F32, F64):
-            ours = codec.get_max_float_compressed_size(ft, n)
-            ours_sp = codec.get_max_sparse_float_compressed_size(ft, n)
+            ours = lib.dgb_float_max_compressed_size(ft, n)
+            ours_sp = lib.dgb_sparse_float_max_compressed_size(ft, n)
             if ours == 0 or ours_sp == 0:
+                with pytest.raises(ValueError):
+                    codec.get_max_sparse_float_compressed_size(ft, n)
                 # the bound does not fit 32 bits: the reference's uint32 sum wraps silently, we refuse (return 0)
                 assert n * codec.WORD_BYTES[ft] > (1 << 31)
                 continue
