@@ -11,7 +11,9 @@ LIB_PATH = os.path.join(_HERE, "libdietgpu_b200.so")
 
 OK = 0
 CHECKSUM_MISMATCH = 1
-ERRORS = {-1: "invalid argument", -2: "CUDA error", -3: "misaligned pointer", -4: "internal error"}
+ERRORS = {-1: "invalid argument", -2: "CUDA error", -3: "misaligned pointer", -4: "internal error",
+          -5: "batch too large for the fixed scratch of the no-allocation entry point"}
+NOALLOC_MAX_BATCH = 32  # DGB_NOALLOC_MAX_BATCH
 
 FLOAT16, BFLOAT16, FLOAT32, FLOAT64 = 1, 2, 3, 4
 
@@ -59,6 +61,8 @@ def _load():
     L.dgb_ans_encode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp]
     L.dgb_ans_decode_host.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp, vp]
     L.dgb_host_release.restype = None
+    L.dgb_decode_batch_noalloc.argtypes = [i, i, u32, vp, vp, vp, vp, vp, vp]
+    L.dgb_decode_batch_noalloc.restype = i
     L.dgb_peer_alloc.argtypes = [sz, vp, vp]
     L.dgb_peer_open.argtypes = [vp, vp]
     L.dgb_peer_close.argtypes = [vp]
@@ -94,7 +98,7 @@ EXPORTS = [
     "dgb_float_compress_split_size", "dgb_float_compress_sparse", "dgb_float_decompress",
     "dgb_float_decompress_split_size", "dgb_float_decompress_sparse", "dgb_float_get_compressed_info",
     "dgb_float_compress_host", "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host",
-    "dgb_host_release", "dgb_peer_alloc", "dgb_peer_open", "dgb_peer_close", "dgb_peer_free",
+    "dgb_host_release", "dgb_decode_batch_noalloc", "dgb_peer_alloc", "dgb_peer_open", "dgb_peer_close", "dgb_peer_free",
 ]
 
 

@@ -12,6 +12,9 @@
 // section. fp64 decodes both exponent planes of the tile before the join, so it is single pass
 // too (the reference always takes two passes for fp64, GpuFloatDecompress.cuh:932-935).
 #include <cstdlib>
+#include <cstring>
+
+#include "../../include/dietgpu_b200.h"
 
 #include "float_math.cuh"
 #include "internal.h"
@@ -693,4 +696,138 @@ int launchDecode(Temp& tmp, const DecodeArgs& a, cudaStream_t s) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// No-allocation decode (dgb_decode_batch_noalloc, include/dietgpu_b200.h). No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it). It is launchDecode above with the decoder's scratch - descriptor table,
+// DecInfo records, expanded LUTs and the tile-claim counter - placed in ONE file-scope device array of fixed size
+// instead of the caller's temp region / the stream-ordered pool, and with the descriptor table shipped as a kernel
+// argument instead of a host-to-device copy. Nothing on this path calls cudaMalloc, cudaFree, cudaMallocAsync,
+// cudaMallocHost or an allocating library routine.
+//
+// Limit: kNoAllocMaxBatch batch elements per call (the scratch does not depend on the elements' sizes).
+// The array is resident on every GPU that loads the library until the process exits (about 0.5 MiB).
+// Every call on a device shares the array and it keeps the previous call's contents: each call rewrites every record
+// it later reads (descriptors by k_noAllocLoadElems, DecInfo + LUT + the claim counter by k_decodePrep), so nothing
+// needs a separate clear - but two calls that OVERLAP on the GPU (different streams, or different host threads
+// without ordering) race on it. Calls on one stream are ordered and safe.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kNoAllocMaxBatch = DGB_NOALLOC_MAX_BATCH; // 32 (include/dietgpu_b200.h)
+constexpr size_t noAllocRound(size_t v) { return (v + 255) / 256 * 256; }
+constexpr size_t kNoAllocElemBytes = noAllocRound((kNoAllocMaxBatch + 1) * sizeof(Elem));
+constexpr size_t kNoAllocInfoBytes = noAllocRound(2 * kNoAllocMaxBatch * sizeof(DecInfo));
+constexpr size_t kNoAllocCounterBytes = 256;
+constexpr size_t kNoAllocLutBytes = (size_t)2 * kNoAllocMaxBatch * (4u << 11); // two planes (fp64), probBits <= 11
+constexpr size_t kNoAllocScratchBytes = kNoAllocElemBytes + kNoAllocInfoBytes + kNoAllocCounterBytes + kNoAllocLutBytes;
+
+// In host code this name is only a stand-in for the symbol, NOT a device address: its address for the current device
+// comes from cudaGetSymbolAddress (noAllocScratch below). Device code could name it directly.
+static __device__ __align__(256) uint8_t g_noAllocScratch[kNoAllocScratchBytes];
+
+struct NoAllocElems {
+  Elem e[kNoAllocMaxBatch + 1];
+};
+
+// descriptor table: kernel argument -> scratch (replaces the H2D copy of the ordinary path)
+__global__ void __launch_bounds__(64) k_noAllocLoadElems(const __grid_constant__ NoAllocElems t, Elem* __restrict__ dst,
+                                                         uint32_t count) {
+  const uint32_t* src = (const uint32_t*)t.e;
+  uint32_t* d = (uint32_t*)dst;
+  for (uint32_t i = threadIdx.x; i < count * (uint32_t)(sizeof(Elem) / 4); i += blockDim.x) d[i] = src[i];
+}
+
+// device address of the scratch array on the CURRENT device; looked up once per device, with that device current
+static int noAllocScratch(uint8_t** out) {
+  static uint8_t* ptrByDev[kMaxDevices] = {};
+  static DeviceOnce once;
+  const int dev = currentDevice();
+  if (once.first(dev)) {
+    uint8_t* ptr = nullptr;
+    DGB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noAllocScratch));
+    if (!ptr) return kErrCuda;
+    __atomic_store_n(&ptrByDev[dev], ptr, __ATOMIC_RELEASE);
+    once.done(dev);
+  }
+  *out = __atomic_load_n(&ptrByDev[dev], __ATOMIC_ACQUIRE);
+  return *out ? kOk : kErrCuda;
+}
+
+int decodeNoAlloc(int ft, int pb, uint32_t num, const void* const* in, void* const* out, const uint32_t* cap,
+                  uint8_t* successDev, uint32_t* sizeDev, cudaStream_t s) {
+  if (num == 0) return kOk;
+  if (!in || !out || !cap || pb < 9 || pb > 11 || ft < kFtNone || ft > kFtF64) return kErrInvalidArg;
+  if (num > kNoAllocMaxBatch) {
+    fprintf(stderr, "dietgpu_b200: dgb_decode_batch_noalloc: %u batch elements exceed the fixed scratch (maximum %u "
+            "per call); split the batch or use the ordinary entry points\n", num, kNoAllocMaxBatch);
+    return kErrTooLarge;
+  }
+  const uint32_t wb = ft == kFtNone ? 1u : floatWordBytes(ft);
+  NoAllocElems tbl;
+  memset(&tbl, 0, sizeof(tbl));
+  uint64_t tiles = 0, plane = 0;
+  for (uint32_t i = 0; i < num; ++i) {
+    if (((uintptr_t)in[i]) & 15u) return kErrAlignment;
+    if (((uintptr_t)out[i]) & (wb - 1)) return kErrAlignment;
+    Elem& e = tbl.e[i];
+    e.in = in[i];
+    e.out = out[i];
+    e.n = cap[i];
+    e.tileBase = (uint32_t)tiles;
+    e.planeOff = plane;
+    const uint32_t t = divUp(cap[i], kTileSyms);
+    tiles += t ? t : 1;
+    plane += roundUpSz(cap[i], 128);
+    if (tiles > 0x7fffffffull) return kErrInvalidArg;
+  }
+  tbl.e[num].tileBase = (uint32_t)tiles; // sentinel
+
+  uint8_t* base = nullptr;
+  int rc = noAllocScratch(&base);
+  if (rc) return rc;
+  Elem* elemsDev = (Elem*)base;
+  DecInfo* info = (DecInfo*)(base + kNoAllocElemBytes);
+  uint32_t* counter = (uint32_t*)(base + kNoAllocElemBytes + kNoAllocInfoBytes);
+  uint32_t* lut = (uint32_t*)(base + kNoAllocElemBytes + kNoAllocInfoBytes + kNoAllocCounterBytes);
+  const int planes = ft == kFtF64 ? 2 : 1;
+  {
+    ProfScope ps__("k_noAllocLoadElems", s);
+    k_noAllocLoadElems<<<1, 64, 0, s>>>(tbl, elemsDev, num + 1);
+  }
+  DGB_CUDA(cudaGetLastError());
+  DecodeArgs a;
+  a.elems = elemsDev;
+  a.numElems = num;
+  a.totalTiles = (uint32_t)tiles;
+  a.floatType = ft;
+  a.sparseNested = 0;
+  a.probBits = pb;
+  a.outSuccess = successDev;
+  a.outSize = sizeDev;
+  a.denseBase = nullptr;
+  {
+    ProfScope ps__("k_decodePrep", s);
+    k_decodePrep<<<dim3(num, planes), 256, 0, s>>>(a, info, lut, counter); // also zeroes the claim counter
+  }
+  DGB_CUDA(cudaGetLastError());
+  DecParams p;
+  p.a = a;
+  p.info = info;
+  p.lut = lut;
+  p.claimTiles = 1;
+  p.tileCounter = counter;
+  switch (pb) {
+    case 9: return launchDecodeFt<9>(p, s);
+    case 10: return launchDecodeFt<10>(p, s);
+    default: return launchDecodeFt<11>(p, s);
+  }
+}
+
 } // namespace dgb
+
+extern "C" int dgb_decode_batch_noalloc(int float_type, int prob_bits, uint32_t num_in_batch, const void* const* in,
+                                        void* const* out, const uint32_t* out_capacity, uint8_t* out_success_dev,
+                                        uint32_t* out_size_dev, void* stream) {
+  return dgb::decodeNoAlloc(float_type, prob_bits, num_in_batch, in, out, out_capacity, out_success_dev, out_size_dev,
+                            (cudaStream_t)stream);
+}

@@ -17,6 +17,7 @@ enum Status : int {
   kErrCuda = -2,
   kErrAlignment = -3,
   kErrInternal = -4,
+  kErrTooLarge = -5, // dgb_decode_batch_noalloc: the batch exceeds the fixed scratch array
   kChecksumMismatch = 1,
 };
 

@@ -40,6 +40,7 @@ extern "C" {
 #define DGB_ERR_CUDA (-2)
 #define DGB_ERR_ALIGNMENT (-3)
 #define DGB_ERR_INTERNAL (-4)
+#define DGB_ERR_TOO_LARGE (-5) /* dgb_decode_batch_noalloc only: batch beyond DGB_NOALLOC_MAX_BATCH */
 
 /* dietgpu::FloatType, dietgpu/float/GpuFloatCodec.h:18-24 */
 #define DGB_FLOAT16 1
@@ -175,6 +176,25 @@ int dgb_ans_decode_host(int prob_bits, int use_checksum, uint32_t num_in_batch, 
                         uint8_t* out_success, uint32_t* out_size, void* stream);
 /* Frees the cached staging buffers and streams of the host-buffer calls (all devices). */
 void dgb_host_release(void);
+
+/* ---- decode without any allocation -------------------------------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Decodes a batch exactly as dgb_ans_decode_batch_pointer (float_type 0 = raw ANS bytes, sizes in bytes) or
+ * dgb_float_decompress (float_type 1..4, sizes in words) do - same `in` / `out` / `out_capacity` host arrays, same
+ * out_success_dev / out_size_dev device arrays (nullable), bit-identical output - but the decoder's scratch
+ * (descriptor table, per-element records, decode tables, work counter) lives in one fixed `static __device__`
+ * array inside the library (about 0.5 MiB, resident on every GPU that loads the library until the process exits),
+ * and the call performs no cudaMalloc / cudaFree / cudaMallocAsync / cudaMallocHost and no allocating library call.
+ *   - at most DGB_NOALLOC_MAX_BATCH batch elements per call, of any size; more returns DGB_ERR_TOO_LARGE (with a
+ *     message on stderr) and launches nothing;
+ *   - no checksum verification (it needs a read-back; use the ordinary entry points for that);
+ *   - all calls on one device share the scratch array: calls ordered on one stream are safe, calls that OVERLAP on
+ *     the GPU (other streams, unordered host threads) race on it and must be serialised by the caller. */
+#define DGB_NOALLOC_MAX_BATCH 32
+int dgb_decode_batch_noalloc(int float_type, int prob_bits, uint32_t num_in_batch, const void* const* in,
+                             void* const* out, const uint32_t* out_capacity, uint8_t* out_success_dev,
+                             uint32_t* out_size_dev, void* stream);
 
 /* ---- peer buffers (compressed collectives inside one NVLink / NVSwitch node) ------------------- */
 /* A device buffer that the other ranks (processes) of the node can map: cudaMalloc + CUDA IPC. A rank
