@@ -104,22 +104,50 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def _cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
 def pin_to_gpu_numa_node(index):
-    """Runs this rank on the CPUs next to its GPU (NVML's ideal affinity), so that the pinned host buffers of the
-    host-buffer leg are first touched, hence placed, on the GPU's own NUMA node. Both arms do this; without it
-    the ranks of a multi-GPU run land on arbitrary nodes and share one memory controller."""
+    """Runs this rank on the CPUs of its GPU's NUMA node, so that the pinned host buffers of the host-buffer leg are
+    first touched, hence placed, next to the GPU. The node comes from the PCI device itself
+    (/sys/bus/pci/devices/<bdf>/numa_node); NVML's "ideal CPU affinity" is only the fallback (on the round-1 pool it
+    reported the same 0-31 mask for all eight GPUs). Both arms do this. Returns what was done, for the JSON line."""
+    info = {"numa_node": None, "cpus": None, "source": None}
     try:
         import pynvml
         pynvml.nvmlInit()
         h = pynvml.nvmlDeviceGetHandleByIndex(index)
-        words = (os.cpu_count() + 63) // 64
-        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
-        cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+        cpus = set()
+        try:
+            bdf = pynvml.nvmlDeviceGetPciInfo(h).busId
+            bdf = (bdf.decode() if isinstance(bdf, bytes) else bdf).lower()
+            if len(bdf.split(":")[0]) == 8:  # NVML prints an 8-digit PCI domain, sysfs a 4-digit one
+                bdf = bdf[4:]
+            node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+            if node >= 0:
+                cpus = _cpulist(open(f"/sys/devices/system/node/node{node}/cpulist").read())
+                info.update(numa_node=node, source="sysfs")
+        except Exception:
+            cpus = set()
+        if not cpus:
+            words = (os.cpu_count() + 63) // 64
+            mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+            cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+            info["source"] = "nvml affinity"
         cpus &= os.sched_getaffinity(0)
         if cpus:
             os.sched_setaffinity(0, cpus)
+            info["cpus"] = len(cpus)
     except Exception:
         pass
+    return info
 
 
 def make_batch(rank):
@@ -230,7 +258,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the product path)")
     torch.cuda.set_device(local_rank)
-    pin_to_gpu_numa_node(local_rank)
+    numa = pin_to_gpu_numa_node(local_rank)
     dist = None
     if world > 1 and (args.impl == "ours" or ref.ok()):
         # the reference's CUDA build shards the batch exactly like ours: one rank per GPU for both arms
@@ -396,7 +424,7 @@ def main():
                    "batch": BATCH, "elem_bytes": ELEM_WORDS * 2, "l2": "inputs (512 MiB) larger than L2",
                    "parallelism": f"batch elements sharded over {n_ranks} GPU(s), no collective"},
         "compression_ratio": round(ratio, 4),
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "host_placement": numa,
         "roofline": roofline, "phases": phase,
     }
     if collective is not None:

@@ -153,79 +153,186 @@ __global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
   }
 }
 
+// ---- decompress: count -> scan -> scatter, three dependency-free launches ---------------------------------------
+// Round 1's single-pass scatter took its tile offsets from a ticket-ordered decoupled look-back: every tile sat on a
+// chain of dependent global round trips (1.5 TB/s). The bitmap is 32 x smaller than the data, so counting it first is
+// nearly free, and then no CTA ever waits for another: sparse fp32 16 x 16 MiB decompress 1475 -> 1782 GB/s on B200.
+// (The same three-launch form for COMPRESS measured slower than k_sparseCompact above, 1049 vs 1231 GB/s: there the
+// count pass has to read all the data a second time.)
+
+// sum of `v` over the CTA's 8 warps (all threads get it); sRed: 8 words
+__device__ __forceinline__ uint32_t ctaSum8(uint32_t v, uint32_t* sRed, uint32_t lane, uint32_t w) {
+  v = warpSum(v);
+  __syncthreads();
+  if (lane == 0) sRed[w] = v;
+  __syncthreads();
+  uint32_t t = 0;
+#pragma unroll
+  for (uint32_t j = 0; j < 8; ++j) t += sRed[j];
+  return t;
+}
+
+// bitmap -> per-tile non-zero counts (1 KB of bitmap per 8192-word tile)
+__global__ void __launch_bounds__(256) k_sparseCountBitmap(const SparseParams p, uint32_t* __restrict__ tileOff) {
+  __shared__ uint32_t sRed[8];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  uint32_t guess = 0;
+  for (uint32_t tk = blockIdx.x; tk < p.totalTiles; tk += gridDim.x) {
+    const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tk, guess);
+    guess = e;
+    const Elem el = p.elems[e];
+    const uint32_t t = tk - el.tileBase;
+    const uint8_t* arch = (const uint8_t*)el.in;
+    const uint32_t n = *(const uint32_t*)arch;
+    uint32_t c = 0;
+    if (el.n >= n) { // capacity ok (else nothing of this element is decoded)
+      const uint32_t stepWord = t * kSpTileWords + tid * 32;
+      if (stepWord < n) c = __popc(((const uint32_t*)(arch + 16))[stepWord >> 5]);
+    }
+    const uint32_t tileTot = ctaSum8(c, sRed, lane, w);
+    if (tid == 0) tileOff[tk] = tileTot;
+  }
+}
+
+// One CTA per element: tile counts -> exclusive offsets in place, 1024 tiles per iteration; also reports
+// success / size (dietgpu/float/GpuSparseFloatDecompress.cuh:119-121: the reported size is the total N).
+__global__ void __launch_bounds__(256) k_sparseScan(const SparseParams p, uint32_t* __restrict__ tileOff) {
+  __shared__ uint32_t sWarp[8];
+  __shared__ uint32_t sCarry;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t e = blockIdx.x;
+  const Elem el = p.elems[e];
+  const uint32_t tb = el.tileBase, T = p.elems[e + 1].tileBase - tb;
+  uint32_t* cnt = tileOff + tb;
+  if (tid == 0) sCarry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < T; base += 1024) {
+    uint32_t c[4];
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) {
+      const uint32_t i = base + tid * 4 + j;
+      c[j] = i < T ? cnt[i] : 0u;
+    }
+    const uint32_t mine = c[0] + c[1] + c[2] + c[3];
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (uint32_t)o) inc += x;
+    }
+    if (lane == 31) sWarp[w] = inc;
+    __syncthreads();
+    uint32_t off = sCarry + inc - mine, total = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j) {
+      const uint32_t x = sWarp[j];
+      off += j < w ? x : 0u;
+      total += x;
+    }
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) {
+      const uint32_t i = base + tid * 4 + j;
+      if (i < T) cnt[i] = off;
+      off += c[j];
+    }
+    __syncthreads();
+    if (tid == 0) sCarry += total;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const uint32_t n = *(const uint32_t*)el.in;
+    if (p.outSuccess) p.outSuccess[e] = el.n >= n ? 1 : 0;
+    if (p.outSize) p.outSize[e] = n;
+  }
+}
+
 template <typename Word>
-__global__ void __launch_bounds__(256) k_sparseScatter(const SparseParams p) {
-  __shared__ uint32_t sTicket, sElem, sExcl;
+__global__ void __launch_bounds__(256) k_sparseScatter(const SparseParams p, const uint32_t* __restrict__ tileOff) {
   __shared__ uint32_t sWarpTot[8];
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const uint32_t ltMask = laneMaskLt();
   uint32_t guess = 0;
-  while (true) {
-    if (tid == 0) {
-      const uint32_t tk = atomicAdd(p.ticket, 1u);
-      sTicket = tk;
-      if (tk < p.totalTiles) sElem = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tk, guess);
-    }
-    __syncthreads();
-    const uint32_t tk = sTicket;
-    if (tk >= p.totalTiles) break;
-    const uint32_t e = sElem;
+  for (uint32_t tk = blockIdx.x; tk < p.totalTiles; tk += gridDim.x) {
+    const uint32_t e = findElement(&p.elems[0].tileBase, sizeof(Elem) / 4, p.numElems, tk, guess);
     guess = e;
     const Elem el = p.elems[e];
     const uint32_t t = tk - el.tileBase;
     const uint8_t* arch = (const uint8_t*)el.in;
     const uint32_t n = *(const uint32_t*)arch; // total words
-    const bool ok = el.n >= n;                 // capacity
-    if (t == 0 && tid == 0) {
-      // dietgpu/float/GpuSparseFloatDecompress.cuh:119-121: the reported size is the total N
-      if (p.outSuccess) p.outSuccess[e] = ok ? 1 : 0;
-      if (p.outSize) p.outSize[e] = n;
-    }
-    if (!ok || t >= divUp(n, kSpTileWords)) {
-      __syncthreads();
-      continue;
-    }
+    if (el.n < n || t >= divUp(n, kSpTileWords)) continue; // capacity too small (reported by the scan) / padding tile
     const uint32_t* bitmap = (const uint32_t*)(arch + 16);
-    const Word* dense = (const Word*)p.dense + el.planeOff;
-    Word* out = (Word*)el.out;
-
+    const Word* __restrict__ dense = (const Word*)p.dense + el.planeOff;
+    Word* __restrict__ out = (Word*)el.out;
     const uint32_t wbase = t * kSpTileWords + w * kSpWarpWords;
     const uint32_t stepWord = wbase + lane * 32;
-    uint32_t myBallot = 0;
+    uint32_t myBallot = 0; // lane k holds the bitmap of step k (32 words)
     if (stepWord < n) myBallot = bitmapToBallot(bitmap[stepWord >> 5]);
     const uint32_t myCount = __popc(myBallot);
     uint32_t inc = myCount;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+      const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= (uint32_t)o) inc += x;
     }
+    __syncthreads(); // previous tile's readers of sWarpTot are done
     if (lane == 31) sWarpTot[w] = inc;
     __syncthreads();
-    uint32_t warpOff = 0, tileTot = 0;
+    uint32_t warpOff = 0;
 #pragma unroll
-    for (uint32_t j = 0; j < 8; ++j) {
-      uint32_t x = sWarpTot[j];
-      warpOff += j < w ? x : 0u;
-      tileTot += x;
-    }
-    if (w == 0) {
-      uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileTot, p.errFlag);
-      if (lane == 0) sExcl = ex;
-    }
-    __syncthreads();
-    const uint32_t stepOff = sExcl + warpOff + inc - myCount;
+    for (uint32_t j = 0; j < 8; ++j) warpOff += j < w ? sWarpTot[j] : 0u;
+    const uint32_t stepOff = tileOff[tk] + warpOff + inc - myCount; // lane k: where step k's non-zeros start
     // the last word lives at idx[N-2] + 1 whatever word N-2 was (GpuSparseFloatDecompress.cuh:127-144)
     bool quirk = false;
     if (n >= 2) quirk = ((((const uint8_t*)bitmap)[(n - 2) >> 3] >> (7 - ((n - 2) & 7))) & 1u) == 0;
-#pragma unroll 8
-    for (uint32_t k = 0; k < kSpSteps; ++k) {
-      uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
-      uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
-      uint32_t i = wbase + k * 32 + lane;
-      Word val = Word(0);
-      if ((b >> lane) & 1u) val = dense[o + __popc(b & ltMask) + ((quirk && i == n - 1) ? 1u : 0u)];
-      if (i < n) out[i] = val;
+    // Full, aligned warp block (the common case): every lane produces 16 bytes per step - W consecutive words, their
+    // non-zeros consecutive in the dense array - and stores them as one vector. (ncu, round 2: the one-word-per-lane
+    // loop below is instruction bound, 25 warp instructions per 32 words at 66 % issue activity.)
+    constexpr uint32_t W = 16 / sizeof(Word);
+    if ((((uintptr_t)out) & 15u) == 0 && wbase + kSpWarpWords <= n && !(quirk && wbase + kSpWarpWords == n)) {
+      uint4* o16 = (uint4*)(out + wbase);
+#pragma unroll
+      for (uint32_t s = 0; s < kSpWarpWords / (32 * W); ++s) {
+        const uint32_t wi = s * 32 * W + lane * W; // first word of this lane inside the warp block
+        const uint32_t g = wi >> 5, off = wi & 31u;  // its 32-word group and position in it
+        const uint32_t b = __shfl_sync(0xffffffffu, myBallot, g);
+        const uint32_t o = __shfl_sync(0xffffffffu, stepOff, g) + __popc(b & ((1u << off) - 1u));
+        const uint32_t bits = (b >> off) & ((1u << W) - 1u);
+        Word v[W];
+#pragma unroll
+        for (uint32_t j = 0; j < W; ++j) {
+          v[j] = Word(0);
+          if ((bits >> j) & 1u) v[j] = __ldg(dense + o + __popc(bits & ((1u << j) - 1u)));
+        }
+        uint4 x;
+        if constexpr (sizeof(Word) == 2) {
+          x = make_uint4((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16),
+                         (uint32_t)v[4] | ((uint32_t)v[5] << 16), (uint32_t)v[6] | ((uint32_t)v[7] << 16));
+        } else if constexpr (sizeof(Word) == 4) {
+          x = make_uint4((uint32_t)v[0], (uint32_t)v[1], (uint32_t)v[2], (uint32_t)v[3]);
+        } else {
+          x = make_uint4((uint32_t)v[0], (uint32_t)((unsigned long long)v[0] >> 32), (uint32_t)v[1],
+                         (uint32_t)((unsigned long long)v[1] >> 32));
+        }
+        o16[s * 32 + lane] = x;
+      }
+      continue;
+    }
+#pragma unroll
+    for (uint32_t k0 = 0; k0 < kSpSteps; k0 += 8) { // the loads of 8 steps are issued before their stores
+      Word v[8];
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint32_t b = __shfl_sync(0xffffffffu, myBallot, k0 + k);
+        const uint32_t o = __shfl_sync(0xffffffffu, stepOff, k0 + k);
+        const uint32_t i = wbase + (k0 + k) * 32 + lane;
+        v[k] = Word(0);
+        if ((b >> lane) & 1u) v[k] = __ldg(dense + o + __popc(b & ltMask) + ((quirk && i == n - 1) ? 1u : 0u));
+      }
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint32_t i = wbase + (k0 + k) * 32 + lane;
+        if (i < n) out[i] = v[k];
+      }
     }
   }
 }
@@ -264,25 +371,44 @@ int launchSparseCompact(Temp& tmp, int ft, const Elem* elems, uint32_t numElems,
   return kOk;
 }
 
+template <typename Word>
+static void scatterLaunch(const SparseParams& p, uint32_t* tileOff, cudaStream_t s) {
+  const uint32_t grid = min(p.totalTiles, (uint32_t)smCount() * 8u);
+  {
+    ProfScope ps__("k_sparseCountBitmap", s);
+    k_sparseCountBitmap<<<grid, 256, 0, s>>>(p, tileOff);
+  }
+  {
+    ProfScope ps__("k_sparseScan", s);
+    k_sparseScan<<<p.numElems, 256, 0, s>>>(p, tileOff);
+  }
+  {
+    ProfScope ps__("k_sparseScatter", s);
+    k_sparseScatter<Word><<<grid, 256, 0, s>>>(p, tileOff);
+  }
+}
+
 int launchSparseScatter(Temp& tmp, int ft, const Elem* elems, uint32_t numElems, uint32_t totalTiles,
                         const uint8_t* dense, uint8_t* outSuccess, uint32_t* outSize, cudaStream_t s) {
   if (!numElems) return kOk;
   SparseParams p;
-  sparseParams(p, tmp, elems, numElems, totalTiles);
-  if (tmp.failed()) return kErrCuda;
+  p.elems = elems;
+  p.numElems = numElems;
+  p.totalTiles = totalTiles;
+  p.tileState = nullptr;
+  p.ticket = nullptr;
+  p.errFlag = nullptr;
+  p.prefetch = 0;
   p.dense = (uint8_t*)dense;
   p.nnz = nullptr;
   p.outSuccess = outSuccess;
   p.outSize = outSize;
-  DGB_CUDA(cudaMemsetAsync(p.tileState, 0, (size_t)totalTiles * 8 + 16, s));
-  uint32_t perSm = 8; // 32 registers: all 64 warps of an SM
-  if (DGB_KNOB("DGB_SPARSE_SCATTER_CTAS", 0) > 0) perSm = (uint32_t)DGB_KNOB("DGB_SPARSE_SCATTER_CTAS", 0); // experiment knob
-  uint32_t grid = min(totalTiles, (uint32_t)smCount() * perSm);
-  ProfScope ps__("k_sparseScatter", s);
+  uint32_t* tileOff = tmp.alloc<uint32_t>((size_t)totalTiles + 4); // counts, then exclusive offsets; fully rewritten per call
+  if (tmp.failed()) return kErrCuda;
   switch (floatWordBytes(ft)) {
-    case 2: k_sparseScatter<uint16_t><<<grid, 256, 0, s>>>(p); break;
-    case 4: k_sparseScatter<uint32_t><<<grid, 256, 0, s>>>(p); break;
-    default: k_sparseScatter<unsigned long long><<<grid, 256, 0, s>>>(p); break;
+    case 2: scatterLaunch<uint16_t>(p, tileOff, s); break;
+    case 4: scatterLaunch<uint32_t>(p, tileOff, s); break;
+    default: scatterLaunch<unsigned long long>(p, tileOff, s); break;
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;

@@ -93,6 +93,21 @@ def run_config(name, kind, ft, ins, counts, steps, sparse=False):
     for i in (0, n - 1):
         assert torch.equal(outs[i], ins[i].view(torch.uint8).reshape(-1)[: counts[i] * wb]), "round trip mismatch"
     Ctot = int(csz.sum())
+    # per-kernel device time (CUDA events around every launch, csrc/prof.cu), 3 extra calls of each direction
+    buf = C.create_string_buffer(1 << 16)
+    _capi.lib.dgb_profile_report(buf, len(buf))  # clear
+    _capi.lib.dgb_profile_enable(1)
+    for _ in range(3):
+        ours_c()
+        ours_d()
+    torch.cuda.synchronize()
+    _capi.lib.dgb_profile_enable(0)
+    _capi.lib.dgb_profile_report(buf, len(buf))
+    kern = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.split()
+        kern[name] = round(float(ms) / 3, 4)
+    res["kernels_ms_per_call"] = kern
     res.update(ratio=round(Ctot / U, 4),
                ours={"compress_GBps": round(U / tc / 1e6, 1), "decompress_GBps": round(U / td / 1e6, 1),
                      "compress_ms": round(tc, 4), "decompress_ms": round(td, 4),
