@@ -405,30 +405,46 @@ def main():
 
     # ---------------- e2e: host buffers through the public op API ----------------
     e2e = None if args.no_e2e else run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks)
+    def build_line(collective):
+        line = {
+            "metric": "compress+decompress GB/s (uncompressed), bf16 float codec",
+            "value": round(value, 2), "unit": "GB/s", "n_gpus": n_ranks, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32 integer (bf16 words)", "data": "synthetic",
+            "config": {"workload": "bf16 float codec, batch 128 x 4 MiB N(0, 0.02) tensors per GPU, probBits 10, "
+                                   "checksum off (BASELINE.json configs[1])",
+                       "batch": BATCH, "elem_bytes": ELEM_WORDS * 2, "l2": "inputs (512 MiB) larger than L2",
+                       "parallelism": f"batch elements sharded over {n_ranks} GPU(s), no collective"},
+            "compression_ratio": round(ratio, 4),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "host_placement": numa,
+            "roofline": roofline, "phases": phase,
+        }
+        if collective is not None:
+            line["collective"] = collective
+        return line
+
     collective = None
     if ref is None and dist is not None and not args.no_collective:
+        # The sharded line must survive whatever the collective leg does: a watchdog thread (it runs even while the
+        # main thread is blocked inside a CUDA / NCCL call) prints the line without the record and ends the process.
+        def give_up():
+            if rank == 0:
+                sys.stdout.write(json.dumps(build_line({"error": "collective leg timed out after 180 s"})) + "\n")
+                sys.stdout.flush()
+            os._exit(0)
+
+        dog = threading.Timer(180.0, give_up)
+        dog.daemon = True
+        dog.start()
         collective = run_collectives(dist, rank, world)
+        dog.cancel()
 
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return 0
 
-    line = {
-        "metric": "compress+decompress GB/s (uncompressed), bf16 float codec",
-        "value": round(value, 2), "unit": "GB/s", "n_gpus": n_ranks, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32 integer (bf16 words)", "data": "synthetic",
-        "config": {"workload": "bf16 float codec, batch 128 x 4 MiB N(0, 0.02) tensors per GPU, probBits 10, "
-                               "checksum off (BASELINE.json configs[1])",
-                   "batch": BATCH, "elem_bytes": ELEM_WORDS * 2, "l2": "inputs (512 MiB) larger than L2",
-                   "parallelism": f"batch elements sharded over {n_ranks} GPU(s), no collective"},
-        "compression_ratio": round(ratio, 4),
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "host_placement": numa,
-        "roofline": roofline, "phases": phase,
-    }
-    if collective is not None:
-        line["collective"] = collective
+    line = build_line(collective)
     if args.impl == "reference":
         line["impl"] = "reference"
         line["reference_kind"] = "reference CUDA build (oracle/_ref/libdietgpu_ref.so) on the GPU"

@@ -67,6 +67,8 @@ def _load():
     L.dgb_peer_open.argtypes = [vp, vp]
     L.dgb_peer_close.argtypes = [vp]
     L.dgb_peer_free.argtypes = [vp]
+    L.dgb_peer_pull_float.argtypes = [u32, vp, vp, vp, u32, vp]
+    L.dgb_peer_pull_float.restype = i
     L.dgb_profile_launches.restype = C.c_ulonglong
     L.dgb_profile_enable.argtypes = [i]
     L.dgb_set_fused_min_tiles.argtypes = [C.c_longlong]
@@ -98,7 +100,7 @@ EXPORTS = [
     "dgb_float_compress_split_size", "dgb_float_compress_sparse", "dgb_float_decompress",
     "dgb_float_decompress_split_size", "dgb_float_decompress_sparse", "dgb_float_get_compressed_info",
     "dgb_float_compress_host", "dgb_float_decompress_host", "dgb_ans_encode_host", "dgb_ans_decode_host",
-    "dgb_host_release", "dgb_decode_batch_noalloc", "dgb_peer_alloc", "dgb_peer_open", "dgb_peer_close", "dgb_peer_free",
+    "dgb_host_release", "dgb_decode_batch_noalloc", "dgb_peer_alloc", "dgb_peer_open", "dgb_peer_close", "dgb_peer_free", "dgb_peer_pull_float",
 ]
 
 

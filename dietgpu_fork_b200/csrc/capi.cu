@@ -98,7 +98,7 @@ WorkRange wholeRange(const WorkList& wl, uint32_t num) {
 // read it has completed (event). The calls read the caller's host arrays at call time, so they are NOT capturable
 // into CUDA graphs (neither are the reference's).
 struct PinnedRing {
-  static constexpr int kSlots = 4;
+  static constexpr int kSlots = 16; // calls that may be enqueued behind a stream wait before the first one ran
   struct Slot {
     void* p = nullptr;
     size_t cap = 0;

@@ -209,6 +209,14 @@ int dgb_peer_alloc(size_t bytes, void** dev_ptr, void* handle64);
 int dgb_peer_open(const void* handle64, void** peer_ptr);
 int dgb_peer_close(void* peer_ptr);
 int dgb_peer_free(void* dev_ptr);
+/* Copies `num` float archives from (peer or local) device memory to local device memory on `stream`; each archive's
+ * length is taken from its own headers ON THE DEVICE (no size exchange, no host synchronisation). src_dev, dst_dev and
+ * dst_capacity_dev are DEVICE arrays of `num` entries (16-byte aligned archives / destinations, capacities in bytes);
+ * max_bytes (host value, an upper bound of any one archive) only sizes the launch. An archive whose headers are not
+ * sane or that does not fit its capacity arrives as a zeroed header, which the decoder reports as failed.
+ * dist.py pulls peer k + 1 on a copy stream while it decodes peer k. No reference counterpart. */
+int dgb_peer_pull_float(uint32_t num, const void* const* src_dev, void* const* dst_dev,
+                        const uint32_t* dst_capacity_dev, uint32_t max_bytes, void* stream);
 
 /* Scratch bytes the last finished call on this thread took (from temp_dev plus the pool): what the
  * reference reports through StackDeviceMemory::getMaxMemoryUsage(),

@@ -67,7 +67,20 @@ def measure(dist_mod, rank, world, mib=64, steps=10, warmup=3, chunks=1, peer=Tr
                        steps, warmup)
         assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather is not bit exact (timed)"
         ag.update({"compressed_peer_ms": round(t_peer, 4), "compressed_peer": round(delivered / t_peer / 1e6, 1),
-                   "peer_vs_raw": round(t_raw / t_peer, 3)})
+                   "peer_vs_raw": round(t_raw / t_peer, 3), "peer_mode": "decoder reads the peers' archives in place"})
+        out.zero_()
+        dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=chunks, temp=temp, mode="pull")
+        torch.cuda.synchronize()
+        assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "pull-mode peer all-gather is not bit exact"
+        t_inp = timed(lambda: dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=chunks, temp=temp,
+                                                             mode="pull"), steps, warmup)
+        ag.update({"compressed_peer_pull_ms": round(t_inp, 4),
+                   "compressed_peer_pull": round(delivered / t_inp / 1e6, 1)})
+        if world > 3:  # fewer, larger pull / decode steps
+            t_s2 = timed(lambda: dgd.all_gather_compressed_peer(shard, peers, out=out, num_chunks=chunks, temp=temp,
+                                                                mode="pull", stages=2), steps, warmup)
+            assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), "peer all-gather (2 stages) is not bit exact"
+            ag.update({"compressed_peer_pull_2stages_ms": round(t_s2, 4)})
     res["all_gather"] = ag
 
     # --- all-to-all: mib/world MiB to every peer ---
@@ -93,6 +106,14 @@ def measure(dist_mod, rank, world, mib=64, steps=10, warmup=3, chunks=1, peer=Tr
         assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "peer all-to-all is not bit exact (timed)"
         aa.update({"compressed_peer_ms": round(t_peer, 4), "compressed_peer": round(delivered / t_peer / 1e6, 1),
                    "peer_vs_raw": round(t_raw / t_peer, 3)})
+        out2.zero_()
+        dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp, mode="pull")
+        torch.cuda.synchronize()
+        assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), "pull-mode peer all-to-all is not bit exact"
+        t_inp = timed(lambda: dgd.all_to_all_compressed_peer(send, peers, out=out2, temp=temp, mode="pull"), steps,
+                      warmup)
+        aa.update({"compressed_peer_pull_ms": round(t_inp, 4),
+                   "compressed_peer_pull": round(delivered / t_inp / 1e6, 1)})
         peers.close()
     res["all_to_all"] = aa
     return res

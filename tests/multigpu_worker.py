@@ -30,15 +30,17 @@ def main():
         shard = (torch.randn(n, device="cuda", generator=g) * (0.02 + 0.01 * rank)).to(torch.bfloat16)
         raw = torch.empty((world, n), dtype=torch.bfloat16, device="cuda")
         dist.all_gather_into_tensor(raw.view(-1), shard)
-        out = dgd.all_gather_compressed_peer(shard, peers, num_chunks=1 + it % 2, temp=temp)
-        assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), f"peer all-gather, call {it}"
+        mode = "inplace" if it == 3 else "pull"  # both forms, interleaved on the same buffers
+        out = dgd.all_gather_compressed_peer(shard, peers, num_chunks=1 + it % 2, temp=temp, mode=mode,
+                                             stages=2 if it == 4 else None)
+        assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), f"peer all-gather ({mode}), call {it}"
         out = dgd.all_gather_compressed(shard, num_chunks=2, codec=cdc)
         assert torch.equal(raw.view(torch.int16), out.view(torch.int16)), f"NCCL-form all-gather, call {it}"
         send = shard[:per * world].view(world, per)
         raw2 = torch.empty_like(send)
         dist.all_to_all_single(raw2.view(-1), send.reshape(-1))
-        out2 = dgd.all_to_all_compressed_peer(send, peers, temp=temp)
-        assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), f"peer all-to-all, call {it}"
+        out2 = dgd.all_to_all_compressed_peer(send, peers, temp=temp, mode=mode)
+        assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), f"peer all-to-all ({mode}), call {it}"
         out2 = dgd.all_to_all_compressed(send, codec=cdc)
         assert torch.equal(raw2.view(torch.int16), out2.view(torch.int16)), f"NCCL-form all-to-all, call {it}"
         if it == 2 and rank == world - 1:

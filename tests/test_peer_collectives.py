@@ -30,7 +30,7 @@ def test_peer_all_gather_and_all_to_all_world1(group_of_one, dtype):
     try:
         for it in range(3):  # both halves, and the first one again
             t = (torch.randn(n, device="cuda") * 0.02).to(dtype)
-            out = dgd.all_gather_compressed_peer(t, peers, num_chunks=3)
+            out = dgd.all_gather_compressed_peer(t, peers, num_chunks=3, mode="inplace" if it == 1 else "pull")
             torch.cuda.synchronize()
             assert out.shape == (1, n)
             assert torch.equal(out[0].view(torch.uint8), t.view(torch.uint8)), f"all-gather round {it}"
