@@ -92,59 +92,17 @@ WorkRange wholeRange(const WorkList& wl, uint32_t num) {
   return WorkRange{0, num, 0, wl.totalTiles, 0, wl.totalBlocks};
 }
 
-// Descriptor tables travel through a small per-thread ring of pinned staging buffers, so that the H2D copy is a
-// true asynchronous DMA from memory that outlives the call (a pageable source is staged synchronously by the
-// runtime, and would be a use-after-free if that ever changed). A slot is reused only after the copy that last
-// read it has completed (event). The calls read the caller's host arrays at call time, so they are NOT capturable
-// into CUDA graphs (neither are the reference's).
-struct PinnedRing {
-  static constexpr int kSlots = 16; // calls that may be enqueued behind a stream wait before the first one ran
-  struct Slot {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaEvent_t ev = nullptr;
-    int dev = -1;
-  } slots[kSlots];
-  int next = 0;
-  // no destructor on purpose: a thread-local destructor may run while the CUDA runtime is being torn down at process
-  // exit; the few KB of pinned memory per calling thread are reclaimed with the context
-  // returns a pinned buffer of at least `bytes`, free for reuse; `after` must be called once the copy is enqueued
-  Slot* acquire(size_t bytes) {
-    Slot& sl = slots[next];
-    next = (next + 1) % kSlots;
-    const int dev = currentDevice();
-    if (sl.ev && sl.dev != dev) { // events belong to a device: start over on a device change
-      cudaEventSynchronize(sl.ev);
-      cudaEventDestroy(sl.ev);
-      sl.ev = nullptr;
-    }
-    if (sl.ev) cudaEventSynchronize(sl.ev);
-    if (sl.cap < bytes) {
-      if (sl.p) cudaFreeHost(sl.p);
-      sl.p = nullptr;
-      sl.cap = 0;
-      const size_t want = roundUpSz(bytes, 4096);
-      if (cudaMallocHost(&sl.p, want) != cudaSuccess) return nullptr;
-      sl.cap = want;
-    }
-    if (!sl.ev) {
-      if (cudaEventCreateWithFlags(&sl.ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-      sl.dev = dev;
-    }
-    return &sl;
-  }
-};
-
+// The descriptor table is shipped with one small pageable-source cudaMemcpyAsync. The CUDA runtime stages a pageable
+// source before the call returns (documented: "the function will return once the pageable buffer has been copied to
+// the staging memory"), so the host vector may die after the call, and for a few KB the driver sends the data inline
+// with the command stream: the first kernel starts 4-10 us sooner than behind a copy-engine DMA from pinned memory
+// (round 2 tried a pinned staging ring here: bf16 32 x 2 MiB compress 0.111 -> 0.121 ms, ANS 16 x 1 MiB 62 -> 64 us;
+// reverted). Consequence: these calls read the caller's host arrays at call time and are NOT capturable into CUDA
+// graphs (neither are the reference's); dgb_decode_batch_noalloc ships its table as a kernel argument instead.
 int upload(Temp& tmp, const WorkList& wl, Elem** dev, cudaStream_t s) {
   *dev = tmp.alloc<Elem>(wl.elems.size());
   if (tmp.failed()) return kErrCuda;
-  static thread_local PinnedRing ring;
-  const size_t bytes = wl.elems.size() * sizeof(Elem);
-  PinnedRing::Slot* sl = ring.acquire(bytes);
-  if (!sl) return kErrCuda;
-  memcpy(sl->p, wl.elems.data(), bytes);
-  DGB_CUDA(cudaMemcpyAsync(*dev, sl->p, bytes, cudaMemcpyHostToDevice, s));
-  DGB_CUDA(cudaEventRecord(sl->ev, s));
+  DGB_CUDA(cudaMemcpyAsync(*dev, wl.elems.data(), wl.elems.size() * sizeof(Elem), cudaMemcpyHostToDevice, s));
   return kOk;
 }
 

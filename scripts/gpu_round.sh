@@ -21,3 +21,11 @@ if [ $rc -eq 0 ]; then
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/${tag}_ncu.log 2>&1
   echo "ncu rc=$?" | tee -a gpurun_out/${tag}_rc.log
 fi
+timeout 600 python scripts/bench_configs.py --steps 20 --only none --custom bf16:1:65536,bf16:1:262144,bf16:8:16384,bf16:16:8192,bf16:32:2048 2>/dev/null | tee gpurun_out/${tag}_configs_medium.jsonl | python -c "
+import sys, json
+for l in sys.stdin:
+    try: d = json.loads(l)
+    except Exception: continue
+    o, r, s = d['ours'], d.get('reference', {}), d.get('speedup', {})
+    print(f\"{d['config'][:36]:36s} ours c {o['compress_GBps']:7.1f} d {o['decompress_GBps']:7.1f} | ref c {r.get('compress_GBps', 0):7.1f} d {r.get('decompress_GBps', 0):7.1f} | x {s.get('compress')} {s.get('decompress')} {s.get('round_trip')}\")
+"
