@@ -17,7 +17,7 @@ tail -3 gpurun_out/${tag}_bench_ref.err
 tail -1 gpurun_out/${tag}_bench.json
 tail -3 gpurun_out/${tag}_bench.err
 if [ $rc -eq 0 ]; then
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/${tag}_ncu.log 2>&1
   echo "ncu rc=$?" | tee -a gpurun_out/${tag}_rc.log
 fi
