@@ -75,7 +75,8 @@ __device__ __forceinline__ void histFlush(uint32_t* sh, uint32_t* gHist, uint32_
 __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elems, uint32_t numElems,
                                                    uint32_t totalTiles, uint32_t tilesPerCta,
                                                    uint32_t* __restrict__ hist, uint32_t* __restrict__ normTilesDone,
-                                                   uint2* __restrict__ normTable, int normProbBits) {
+                                                   uint2* __restrict__ normTable, int normProbBits,
+                                                   uint32_t* __restrict__ checksumAcc) {
   __shared__ uint32_t sh[8 * 256 * kHistRep];
   __shared__ uint32_t sLast;
   const uint32_t tid = threadIdx.x;
@@ -87,10 +88,12 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
   uint32_t t0 = blockIdx.x * tilesPerCta;
   uint32_t t1 = min(t0 + tilesPerCta, totalTiles);
   uint32_t cur = 0xffffffffu;
+  uint32_t ck = 0; // checksum folded into this pass (every byte of a raw ANS input counts); flushed per element
   // counts of element `cur` -> global bins; the CTA whose tiles complete the element also builds its encode table
   // (saves the k_normalize launch: small batches are launch-latency bound)
   auto finishElement = [&]() {
     histFlush(sh, hist + cur * 256, tid);
+    if (checksumAcc) ckFlushWarp(ck, checksumAcc + cur);
     if (normTilesDone) {
       const uint32_t eb = elems[cur].tileBase, ee = elems[cur + 1].tileBase;
       __threadfence();
@@ -127,8 +130,14 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
     const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
     // head / tail bytes
     uint32_t headN = (uint32_t)(a0 - p), tailN = (uint32_t)(end - a1);
-    if (tid < headN) histAdd(wh, p[tid], rep);
-    if (tid >= 32 && tid - 32 < tailN) histAdd(wh, a1[tid - 32], rep);
+    if (tid < headN) {
+      histAdd(wh, p[tid], rep);
+      ck ^= p[tid];
+    }
+    if (tid >= 32 && tid - 32 < tailN) {
+      histAdd(wh, a1[tid - 32], rep);
+      ck ^= a1[tid - 32];
+    }
     const uint4* v = (const uint4*)a0;
     uint32_t nvec = (uint32_t)(a1 - a0) >> 4;
     uint32_t i = tid;
@@ -138,24 +147,27 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
       histAddWord(wh, x1.x, rep); histAddWord(wh, x1.y, rep); histAddWord(wh, x1.z, rep); histAddWord(wh, x1.w, rep);
       histAddWord(wh, x2.x, rep); histAddWord(wh, x2.y, rep); histAddWord(wh, x2.z, rep); histAddWord(wh, x2.w, rep);
       histAddWord(wh, x3.x, rep); histAddWord(wh, x3.y, rep); histAddWord(wh, x3.z, rep); histAddWord(wh, x3.w, rep);
+      ck ^= x0.x ^ x0.y ^ x0.z ^ x0.w ^ x1.x ^ x1.y ^ x1.z ^ x1.w ^ x2.x ^ x2.y ^ x2.z ^ x2.w ^ x3.x ^ x3.y ^ x3.z ^ x3.w;
     }
     for (; i < nvec; i += 256) {
       uint4 x0 = v[i];
       histAddWord(wh, x0.x, rep); histAddWord(wh, x0.y, rep); histAddWord(wh, x0.z, rep); histAddWord(wh, x0.w, rep);
+      ck ^= x0.x ^ x0.y ^ x0.z ^ x0.w;
     }
   }
   if (cur != 0xffffffffu) finishElement();
 }
 
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s,
-                    uint32_t* normTilesDone, uint2* normTable, int normProbBits) {
+                    uint32_t* normTilesDone, uint2* normTable, int normProbBits, uint32_t* checksumAcc) {
   if (!totalTiles) return kOk;
   uint32_t ctas = min(totalTiles, (uint32_t)smCount() * 4u);
   uint32_t per = divUp(totalTiles, ctas);
   ctas = divUp(totalTiles, per);
   {
     ProfScope ps__("k_histBytes", s);
-    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist, normTilesDone, normTable, normProbBits);
+    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist, normTilesDone, normTable, normProbBits,
+                                      checksumAcc);
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;

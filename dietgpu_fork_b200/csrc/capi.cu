@@ -180,10 +180,14 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
     DGB_CUDA(cudaMemsetAsync(ownHist, 0, (size_t)num * 1024, s));
     hist = ownHist;
   }
+  // The checksum rides the histogram pass (one XOR per loaded vector, one atomicXor per warp and element) whenever
+  // that pass runs; only a caller-supplied histogram leaves no pass over the data and keeps the separate k_checksum.
+  const bool foldCk = useChecksum && ownHist && DGB_KNOB("DGB_FOLD_CHECKSUM", 1) != 0;
   if (useChecksum) {
     checksum = tmp.alloc<uint32_t>(num);
     if (tmp.failed()) return kErrCuda;
-    if ((rc = launchChecksum(elemsDev, num, wl.maxN, 1, nullptr, 0, checksum, s))) return rc;
+    if (foldCk) DGB_CUDA(cudaMemsetAsync(checksum, 0, sizeof(uint32_t) * num, s));
+    else if ((rc = launchChecksum(elemsDev, num, wl.maxN, 1, nullptr, 0, checksum, s))) return rc;
   }
   EncodeArgs a;
   a.elems = elemsDev;
@@ -200,10 +204,10 @@ int ansEncode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
   a.useChecksum = useChecksum ? 1 : 0;
   EncodeScratch es;
   if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es, s))) return rc;
-  if (fused) return launchFusedCompress(kFtNone, a, es, wl.totalTiles, nullptr, 0, s);
+  if (fused) return launchFusedCompress(kFtNone, a, es, wl.totalTiles, foldCk ? checksum : nullptr, 0, s, foldCk);
   // separate launches: the histogram kernel also builds the tables (unless the caller supplied histograms)
   if (ownHist && (rc = launchHistogram(elemsDev, num, wl.totalTiles, ownHist, s, es.fusedCtrl + kFusedCtrlFixed,
-                                       es.table, pb)))
+                                       es.table, pb, foldCk ? checksum : nullptr)))
     return rc;
   return launchAnsEncode(a, es, wholeRange(wl, num), s, ownHist != nullptr);
 }
@@ -312,11 +316,22 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
   if (tmp.failed()) return kErrCuda;
   DGB_CUDA(cudaMemsetAsync(hist, 0, (size_t)planes * num * 1024, s));
   int rc;
+  // Split is HBM-bound, the encoder issue-bound: cut the batch into element groups and run
+  // split(g + 1) on a side stream while the caller's stream encodes group g.
+  int groups = overlapGroups();
+  cudaStream_t side = nullptr;
+  if (num < 8 || wl.totalTiles < 1024 || planes > 1) groups = 1;
+  if (groups > 1) side = sideStream();
+  if (!side) groups = 1;
+  // The checksum rides the split pass (the CTA completing an element patches its header); the grouped schedule has
+  // no completion protocol and keeps the separate k_checksum pass.
+  const bool foldCk = useChecksum && groups == 1 && DGB_KNOB("DGB_FOLD_CHECKSUM", 1) != 0;
   if (useChecksum) {
     // the float-level checksum covers the first N BYTES of the N-word input
     // (dietgpu/float/GpuFloatCompress.cuh:708-710 with dietgpu/ans/GpuChecksum.cuh:95-102)
     if (denseIn) return kErrInvalidArg; // sparse + checksum: not supported (reference: untested)
-    if ((rc = launchChecksum(elemsDev, num, wl.maxN, 1, nDev, 0, checksum, s))) return rc;
+    if (foldCk) DGB_CUDA(cudaMemsetAsync(checksum, 0, sizeof(uint32_t) * num, s));
+    else if ((rc = launchChecksum(elemsDev, num, wl.maxN, 1, nDev, 0, checksum, s))) return rc;
   }
   EncodeArgs args[2];
   EncodeScratch es[2];
@@ -337,13 +352,6 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     if ((rc = allocEncodeScratch(tmp, a, wl.totalGroups, es[r], s))) return rc;
   }
 
-  // Split is HBM-bound, the encoder issue-bound: cut the batch into element groups and run
-  // split(g + 1) on a side stream while the caller's stream encodes group g.
-  int groups = overlapGroups();
-  cudaStream_t side = nullptr;
-  if (num < 8 || wl.totalTiles < 1024 || planes > 1) groups = 1;
-  if (groups > 1) side = sideStream();
-  if (!side) groups = 1;
   std::vector<WorkRange> ranges;
   {
     uint32_t e0 = 0;
@@ -365,13 +373,13 @@ int floatCompressCore(Temp& tmp, int ft, int pb, int useChecksum, const WorkList
     return launchFloatSplit(ft, elemsDev, num, r.tile0, r.tile1, nDev, denseIn, plane, plane + planeBytes, hist,
                             hist + (size_t)num * 256, checksum, useChecksum, st,
                             withTables ? es[0].fusedCtrl + kFusedCtrlFixed : nullptr, es[0].table,
-                            planes == 2 ? es[1].table : nullptr, pb, minElemTiles);
+                            planes == 2 ? es[1].table : nullptr, pb, minElemTiles, foldCk && withTables);
   };
   if (ranges.size() <= 1) {
     const WorkRange all = wholeRange(wl, num);
     if (planes == 1 && !nDev && !denseIn && num >= kFusedMinElems && fusedWanted(wl.totalTiles, num) &&
         fusedCompressEnabled())
-      return launchFusedCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s);
+      return launchFusedCompress(ft, args[0], es[0], wl.totalTiles, checksum, useChecksum, s, foldCk);
     if ((rc = split(all, s, true))) return rc; // the split kernel also builds the encode tables
     for (int r = 0; r < planes; ++r)
       if ((rc = launchAnsEncode(args[r], es[r], all, s, true))) return rc;

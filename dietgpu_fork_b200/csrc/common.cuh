@@ -113,6 +113,49 @@ __device__ __forceinline__ void bulkLoad(uint32_t dst, const void* src, uint32_t
                : "memory");
 }
 
+// ---- checksum folded into the pass that reads the data anyway -------------------------------------------------
+// The reference's checksum is the XOR of the covered bytes folded to 8 bits (dietgpu/ans/GpuChecksum.cuh:26-133), so
+// any 32-bit XOR accumulation works whatever the alignment, as long as all four byte lanes are folded at the end.
+// `covered` = number of leading bytes of the element that count (all of them for raw ANS; the first N BYTES of the
+// N-word input for the float codecs: dietgpu/float/GpuFloatCompress.cuh:708-710).
+// ckVec: the 16 bytes at byte offset 16 * g of the element.
+__device__ __forceinline__ void ckVec(uint32_t& ck, uint4 x, uint32_t g, uint32_t covered) {
+  const uint32_t full = covered >> 4;
+  if (g < full) {
+    ck ^= x.x ^ x.y ^ x.z ^ x.w;
+  } else if (g == full) {
+    const int k = (int)(covered & 15u); // leading bytes of this vector that count
+    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int kb = k - 4 * j;
+      if (kb >= 4) ck ^= w[j];
+      else if (kb > 0) ck ^= w[j] & ((1u << (8 * kb)) - 1u);
+    }
+  }
+}
+// ckWord: one `bytes`-wide little-endian word at byte offset `off` of the element
+__device__ __forceinline__ void ckWord(uint32_t& ck, unsigned long long v, uint32_t bytes, unsigned long long off,
+                                       uint32_t covered) {
+  if (off >= covered) return;
+  const unsigned long long left = covered - off;
+  if (left < bytes) v &= (1ull << (8 * left)) - 1ull;
+  ck ^= (uint32_t)v ^ (uint32_t)(v >> 32);
+}
+__device__ __forceinline__ uint32_t ckFold8(uint32_t ck) {
+  ck ^= ck >> 16;
+  ck ^= ck >> 8;
+  return ck & 0xffu;
+}
+// warp-reduces the lanes' accumulators and adds the folded result to the element's checksum word; clears ck
+__device__ __forceinline__ void ckFlushWarp(uint32_t& ck, uint32_t* dst) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ck ^= __shfl_xor_sync(0xffffffffu, ck, o);
+  const uint32_t f = ckFold8(ck);
+  if (laneId() == 0 && f) atomicXor(dst, f);
+  ck = 0;
+}
+
 // ---- decoupled look-back tile state ------------------------------------------------------
 // One 64-bit word per tile: [63:62] flag, [31:0] value. A single 8-byte store publishes flag and
 // value together, so no fence is needed between them.

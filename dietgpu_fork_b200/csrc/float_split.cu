@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
     uStep = b1 - b0;
   }
   uint32_t cur = 0xffffffffu, acc = 0; // element whose counts are in the bins, units of it done by this CTA
+  uint32_t ck = 0;                     // this thread's share of the element's checksum (folded pass, SplitParams)
   __shared__ uint32_t sLast;
   // this CTA's counts of element `cur` go to the global bins; if they were the element's last, its table(s) follow
   auto finishElement = [&]() {
@@ -47,12 +48,17 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
     if (kPlanes == 2) splitHistFlush<256>(sh + kHistWords, p.hist1 + cur * 256, tid);
     if (p.normTilesDone) {
       const uint32_t eb = p.elems[cur].tileBase, ee = p.elems[cur + 1].tileBase;
+      if (p.checksumAcc) ckFlushWarp(ck, p.checksumAcc + cur); // before the fence, like the histogram
       __threadfence();
       __syncthreads();
       if (tid == 0) sLast = atomicAdd(&p.normTilesDone[cur], acc) + acc == (ee - eb) << unitShift ? 1u : 0u;
       __syncthreads();
       if (sLast) {
         __threadfence();
+        if (p.checksumAcc && tid == 0) { // every CTA's share is in: the float header gets its checksum
+          uint8_t* fbase = (uint8_t*)p.elems[cur].out + p.elems[cur].sizeBias;
+          ((uint32_t*)fbase)[3] = __ldcg(p.checksumAcc + cur);
+        }
         const uint32_t total = p.nDev ? p.nDev[cur] : p.elems[cur].n;
         normalizeElement<256>(p.hist0 + (size_t)cur * 256, total, p.normProbBits, p.normTable0 + (size_t)cur * 256, sh);
         if (kPlanes == 2)
@@ -73,7 +79,7 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
     }
     const Elem el = p.elems[e];
     const uint32_t n = p.nDev ? p.nDev[e] : el.n;
-    splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh, unitWords, u & (perTile - 1u));
+    splitTile<FT, 256, PIPE>(p, e, el, n, tile, sh, unitWords, u & (perTile - 1u), &ck);
     ++acc;
   }
   if (cur != 0xffffffffu) finishElement();
@@ -138,7 +144,7 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
                      uint32_t* normTilesDone, uint2* normTable0, uint2* normTable1, int normProbBits,
-                     uint32_t minElemTiles) {
+                     uint32_t minElemTiles, bool foldChecksum) {
   if (tileEnd <= tileBegin) return kOk;
   SplitParams p;
   p.elems = elems;
@@ -154,6 +160,7 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
   p.hist1 = hist1;
   p.checksum = checksum;
   p.useChecksum = useChecksum;
+  p.checksumAcc = (foldChecksum && useChecksum && normTilesDone) ? (uint32_t*)checksum : nullptr;
   p.normTilesDone = normTilesDone;
   p.normTable0 = normTable0;
   p.normTable1 = normTable1;

@@ -34,8 +34,12 @@ struct SplitParams {
   uint8_t* plane1;
   uint32_t* hist0;          // [numElems][256]
   uint32_t* hist1;
-  const uint32_t* checksum; // nullable
+  const uint32_t* checksum; // nullable: checksums computed beforehand (k_checksum)
   int useChecksum;
+  // nullable, zeroed [numElems]: the split pass itself accumulates the checksum (one XOR per loaded vector) and the
+  // CTA that completes an element writes it into the float header; needs the completion protocol (normTilesDone in
+  // k_floatSplit, always in the fused kernel). When set, `checksum` is ignored.
+  uint32_t* checksumAcc;
   // stand-alone kernel: when set, the CTA whose tiles complete an element's histogram(s) also builds its encode
   // table(s) - the k_normalize launch disappears from small batches, which are launch-latency bound
   uint32_t* normTilesDone;  // nullable; zeroed [numElems]
@@ -94,7 +98,8 @@ __device__ __forceinline__ void splitHistGroup(uint32_t* wh0, uint32_t* wh1, con
 // CTA's histogram bins (kPlanes * splitHistWords<NT>() words, zeroed by the caller).
 template <int FT, int NT, bool PIPE = true>
 __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, const Elem& el, uint32_t n, uint32_t tile,
-                                          uint32_t* sh, uint32_t sliceWords = kTileSyms, uint32_t slice = 0) {
+                                          uint32_t* sh, uint32_t sliceWords = kTileSyms, uint32_t slice = 0,
+                                          uint32_t* ckAcc = nullptr) {
   using Tr = FloatTraits<FT>;
   using Word = typename Tr::Word;
   constexpr uint32_t G = Tr::kGroup;
@@ -110,7 +115,7 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
   if (t == 0 && slice == 0 && tid == 0) {
     // GpuFloatHeader + GpuFloatHeader2 (dietgpu/float/GpuFloatUtils.cuh:19-96); the second
     // header's firstCompSegmentBytes is filled in by the encoder
-    uint32_t cs = (p.useChecksum && p.checksum) ? p.checksum[e] : 0u;
+    uint32_t cs = (p.useChecksum && p.checksum && !p.checksumAcc) ? p.checksum[e] : 0u; // folded: patched at completion
     ((uint4*)fbase)[0] = make_uint4(kFloatMagic, n, (uint32_t)FT | (p.useChecksum ? 16u : 0u), cs);
     ((uint4*)fbase)[1] = make_uint4(0u, 0u, 0u, 0u);
   }
@@ -120,6 +125,9 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
   uint8_t* plane0 = p.plane0 + el.planeOff;
   uint8_t* plane1 = kPlanes == 2 ? p.plane1 + el.planeOff : plane0;
   const RawSections rs = rawSections(FT, fbase + kFloatHeaderBytes, n);
+  // checksum folded into this pass: the first n BYTES of the n-word input count (0: off)
+  const uint32_t covered = (ckAcc && p.checksumAcc) ? n : 0u;
+  uint32_t ck = 0;
 
   uint32_t vecWords = 0;
   if ((((uintptr_t)in) & 15u) == 0) {
@@ -135,6 +143,7 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           uint32_t ex[2], ex1[2];
+          if (covered) ckVec(ck, x[k], g0 + i + NT * k, covered);
           splitGroup<FT>(x[k], g0 + i + NT * k, plane0, plane1, rs, ex, ex1);
           splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
         }
@@ -159,6 +168,10 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
           y1 = v[j + NT];
         }
         uint32_t ex[2], ex1[2];
+        if (covered) {
+          ckVec(ck, x0, g0 + i, covered);
+          ckVec(ck, x1, g0 + i + NT, covered);
+        }
         splitGroup<FT>(x0, g0 + i, plane0, plane1, rs, ex, ex1);
         splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
         splitGroup<FT>(x1, g0 + i + NT, plane0, plane1, rs, ex, ex1);
@@ -171,7 +184,9 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     }
     for (; i < ng; i += NT) {
       uint32_t ex[2], ex1[2];
-      splitGroup<FT>(v[i], g0 + i, plane0, plane1, rs, ex, ex1);
+      const uint4 xv = v[i];
+      if (covered) ckVec(ck, xv, g0 + i, covered);
+      splitGroup<FT>(xv, g0 + i, plane0, plane1, rs, ex, ex1);
       splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
     }
     vecWords = ng * G;
@@ -179,10 +194,13 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
   // scalar path: whole tile for inputs that are not 16-byte aligned, else the tail
   for (uint32_t i = vecWords + tid; i < len; i += NT) {
     uint32_t e0, e1;
+    if (covered) ckWord(ck, (unsigned long long)((const Word*)in)[off + i], sizeof(Word),
+                        (unsigned long long)(off + i) * sizeof(Word), covered);
     splitScalar<FT>(in, off + i, plane0, plane1, rs, e0, e1);
     splitHistAdd(wh0, e0, rep);
     if (kPlanes == 2) splitHistAdd(wh1, e1, rep);
   }
+  if (covered) *ckAcc ^= ck;
   // zero the section padding after the last word (undefined in the reference)
   if (off + len == n && tid < 16) {
     const uint32_t i = n + tid;

@@ -66,7 +66,7 @@ constexpr uint32_t kFusedSmem =
 // Byte histogram of one 32768-byte tile into the CTA's per-warp replicated bins.
 template <int NT>
 __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t sliceBytes,
-                                              uint32_t* sh) {
+                                              uint32_t* sh, uint32_t* ckAcc) {
   const uint32_t tid = threadIdx.x;
   uint32_t* wh = sh + (tid >> 5) * 256 * kSplitRep;
   const uint32_t rep = tid & (kSplitRep - 1);
@@ -76,8 +76,15 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
   const uint8_t* a0 = (const uint8_t*)(((uintptr_t)q + 15) & ~(uintptr_t)15);
   if (a0 > end) a0 = end;
   const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
-  if (tid < (uint32_t)(a0 - q)) splitHistAdd(wh, q[tid], rep);
-  if (tid >= 32 && tid - 32 < (uint32_t)(end - a1)) splitHistAdd(wh, a1[tid - 32], rep);
+  uint32_t ck = 0; // raw ANS: every byte counts
+  if (tid < (uint32_t)(a0 - q)) {
+    splitHistAdd(wh, q[tid], rep);
+    ck ^= q[tid];
+  }
+  if (tid >= 32 && tid - 32 < (uint32_t)(end - a1)) {
+    splitHistAdd(wh, a1[tid - 32], rep);
+    ck ^= a1[tid - 32];
+  }
   const uint4* v = (const uint4*)a0;
   const uint32_t nvec = (uint32_t)(a1 - a0) >> 4;
   auto addWord = [&](uint32_t x) {
@@ -94,12 +101,15 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       addWord(x[k].x); addWord(x[k].y); addWord(x[k].z); addWord(x[k].w);
+      ck ^= x[k].x ^ x[k].y ^ x[k].z ^ x[k].w;
     }
   }
   for (; i < nvec; i += NT) {
     const uint4 x = __ldg(v + i);
     addWord(x.x); addWord(x.y); addWord(x.z); addWord(x.w);
+    ck ^= x.x ^ x.y ^ x.z ^ x.w;
   }
+  if (ckAcc) *ckAcc ^= ck;
 }
 
 // Between runs (batches of few huge elements only, where compaction would otherwise be a serial tail after the
@@ -155,10 +165,12 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     const uint32_t sliceShift = p.sliceShift, sliceWords = kTileSyms >> sliceShift;
     const uint32_t totalSlices = p.totalTiles << sliceShift;
     uint32_t guess = 0, accElem = 0xffffffffu, accSlices = 0;
+    uint32_t ck = 0; // this thread's share of the element's checksum when the pass is folded (SplitParams::checksumAcc)
     auto publish = [&]() { // all threads
       __syncthreads();
       splitHistFlush<kFusedThreads>(sh, p.sp.hist0 + (size_t)accElem * 256, tid);
-      __threadfence(); // plane, raw bytes and histogram of these slices before the slice count
+      if (p.sp.checksumAcc) ckFlushWarp(ck, p.sp.checksumAcc + accElem);
+      __threadfence(); // plane, raw bytes, histogram and checksum share of these slices before the slice count
       __syncthreads();
       if (tid == 0) {
         const uint32_t want = (p.sp.elems[accElem + 1].tileBase - p.sp.elems[accElem].tileBase) << sliceShift;
@@ -168,6 +180,10 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
       __syncthreads();
       if (sBcast[1]) { // this CTA completed the element: its histogram is final
         __threadfence();
+        if (FT != kFtNone && p.sp.checksumAcc && tid == 0) { // ... and so is its checksum: into the float header
+          uint8_t* fbase = (uint8_t*)p.sp.elems[accElem].out + p.sp.elems[accElem].sizeBias;
+          ((uint32_t*)fbase)[3] = __ldcg(p.sp.checksumAcc + accElem);
+        }
         normalizeElement<kFusedThreads>(p.sp.hist0 + (size_t)accElem * 256, p.sp.elems[accElem].n, PB,
                                         p.ep.table + (size_t)accElem * 256, normSm);
         __threadfence();
@@ -225,9 +241,9 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
         const uint32_t words = whole ? kTileSyms : sliceWords;
         if constexpr (FT == kFtNone) {
           const uint32_t off = (tile - el.tileBase) * kTileSyms + sub * sliceWords;
-          histTileBytes<kFusedThreads>((const uint8_t*)el.in, el.n, off, words, sh);
+          histTileBytes<kFusedThreads>((const uint8_t*)el.in, el.n, off, words, sh, p.sp.checksumAcc ? &ck : nullptr);
         } else {
-          splitTile<FT, kFusedThreads>(p.sp, e, el, el.n, tile, sh, words, whole ? 0u : sub);
+          splitTile<FT, kFusedThreads>(p.sp, e, el, el.n, tile, sh, words, whole ? 0u : sub, &ck);
         }
         const uint32_t step = whole ? perTile : 1u;
         accSlices += step;
@@ -374,7 +390,7 @@ static int launchFusedPb(FusedParams& p, int pb, cudaStream_t s) {
 }
 
 int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
-                             const uint32_t* checksum, int useChecksum, cudaStream_t s) {
+                             const uint32_t* checksum, int useChecksum, cudaStream_t s, bool foldChecksum) {
   if (a.numElems == 0) return kOk;
   if (a.probBits < 9 || a.probBits > 11) return kErrInvalidArg;
   if (a.nDev || ft == kFtF64) return kErrInvalidArg;
@@ -397,6 +413,7 @@ int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, ui
   p.sp.hist1 = nullptr;
   p.sp.checksum = checksum;
   p.sp.useChecksum = useChecksum;
+  p.sp.checksumAcc = foldChecksum ? (uint32_t*)checksum : nullptr;
   p.sp.normTilesDone = nullptr;
   p.sp.normTable0 = p.sp.normTable1 = nullptr;
   p.sp.normProbBits = 0;

@@ -176,11 +176,14 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
 int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s);
 // float split (ft == kFtNone: byte histogram of the raw input) + table normalisation + block encoding +
 // compaction in ONE persistent launch. Single-plane float types or raw ANS, host-known sizes, dense input (fused.cu).
+// foldChecksum: `checksum` is a zeroed array the kernel accumulates into (no k_checksum pass beforehand)
 int launchFusedCompress(int ft, const EncodeArgs& a, const EncodeScratch& es, uint32_t totalTiles,
-                             const uint32_t* checksum, int useChecksum, cudaStream_t s);
+                             const uint32_t* checksum, int useChecksum, cudaStream_t s, bool foldChecksum = false);
 // normTilesDone (nullable, zeroed [numElems]): the CTA completing an element's histogram also builds its table
+// checksumAcc (nullable, zeroed [numElems]): the histogram pass also accumulates the checksum of every element
 int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, uint32_t* hist, cudaStream_t s,
-                    uint32_t* normTilesDone = nullptr, uint2* normTable = nullptr, int normProbBits = 0);
+                    uint32_t* normTilesDone = nullptr, uint2* normTable = nullptr, int normProbBits = 0,
+                    uint32_t* checksumAcc = nullptr);
 // XOR-fold checksum of the first n * bytesPerUnit bytes of every element's input (useOut = 0) or
 // output (useOut = 1); n = nDev[e] when given, else Elem::n. maxUnits bounds n.
 int launchChecksum(const Elem* elems, uint32_t numElems, uint32_t maxUnits, uint32_t bytesPerUnit,
@@ -191,7 +194,7 @@ int launchFloatSplit(int ft, const Elem* elems, uint32_t numElems, uint32_t tile
                      const uint8_t* denseIn, uint8_t* plane0, uint8_t* plane1, uint32_t* hist0,
                      uint32_t* hist1, const uint32_t* checksum, int useChecksum, cudaStream_t s,
                      uint32_t* normTilesDone = nullptr, uint2* normTable0 = nullptr, uint2* normTable1 = nullptr,
-                     int normProbBits = 0, uint32_t minElemTiles = 0);
+                     int normProbBits = 0, uint32_t minElemTiles = 0, bool foldChecksum = false);
 
 struct DecodeArgs {
   const Elem* elems; // device, numElems + 1 (tiles sized from capacities)

@@ -321,3 +321,62 @@ def test_max_compressed_sizes_match_reference_build():
                 continue
             assert ours == L.ref_float_max_compressed_size(ft, n), f"float bound ft {ft} at {n}"
             assert ours_sp == L.ref_sparse_float_max_compressed_size(ft, n), f"sparse bound ft {ft} at {n}"
+
+
+# ------------------------------------------------------------------------------------ checksum folded into the data pass
+@pytest.mark.parametrize("ft", [F16, BF16, F32, F64])
+@pytest.mark.parametrize("big", [False, True], ids=["separate_launches", "fused_kernel"])
+def test_float_checksum_rides_the_split_pass(ft, big):
+    """useChecksum: the checksum (first N BYTES of the N-word input, dietgpu/float/GpuFloatCompress.cuh:708-710) is
+    accumulated by the split pass itself and patched into the header by the CTA that completes the element; no
+    k_checksum launch. Sizes put the end of the covered bytes inside a 16-byte vector, at a vector boundary, in the
+    first tile and tiles later; a misaligned input takes the scalar path."""
+    counts = [0, 1, 13, 16, 4099, 70001, (1 << 20) + 5, 32768 * 3]
+    if big:
+        counts += [(2 << 20) - 7 * i for i in range(16)]  # >= 1024 tiles and >= 16 elements: the fused kernel (not fp64)
+    host = [datagen.float_words(ft, c, seed=600 + i) for i, c in enumerate(counts)]
+    wb = host[0].dtype.itemsize
+    for mis in (0, wb):
+        dev = [H.to_dev(h, mis) for h in host]
+        _kernels_run()  # clear
+        m, sz = H.ours_float_compress(ft, dev, counts, 10, checksum=True)
+        ran = _kernels_run()
+        assert "k_checksum" not in ran, f"the separate checksum pass ran: {ran}"
+        if big and ft != F64:
+            assert "k_compressFused" in ran, ran
+        for i, h in enumerate(host):
+            exp = oracle.float_compress(ft, h, 10, use_checksum=True)
+            got = H.row_bytes(m, i, sz[i])
+            assert got.size == exp.size and np.array_equal(got, exp), f"archive {i} (misalign {mis}) differs from the oracle"
+        outs, ok, dsz = H.ours_float_decompress(ft, [m[i] for i in range(len(counts))], counts, 10, checksum=True)
+        assert ok.all() and list(dsz) == counts
+        if H.ref_lib() is not None and mis == 0:
+            rm, rsz = H.ref_float_compress(ft, dev, counts, 10, checksum=True)
+            H.assert_rows_match_ref(m, sz, rm, rsz, oracle.float_defined_mask, f"checksum ft {ft}")
+
+
+@pytest.mark.parametrize("big", [False, True], ids=["separate_launches", "fused_kernel"])
+def test_ans_checksum_rides_the_histogram_pass(big):
+    sizes = [0, 1, 15, 4097, 70001, (1 << 20) + 3]
+    if big:
+        sizes += [(2 << 20) - 5 * i for i in range(16)]
+    host = [datagen.exp_bytes(n, 20.0, seed=700 + i) for i, n in enumerate(sizes)]
+    for mis in (0, 3):
+        dev = [H.to_dev(h, mis) for h in host]
+        _kernels_run()
+        m, sz = H.ours_ans_encode(dev, 10, checksum=True)
+        ran = _kernels_run()
+        assert "k_checksum" not in ran, f"the separate checksum pass ran: {ran}"
+        for i, h in enumerate(host):
+            exp = oracle.ans_encode(h, 10, use_checksum=True)
+            assert np.array_equal(H.row_bytes(m, i, sz[i]), exp), f"ANS archive {i} (misalign {mis}) differs from the oracle"
+        outs, ok, _ = H.ours_ans_decode([m[i] for i in range(len(sizes))], sizes, 10, checksum=True)
+        assert ok.all()
+    # a caller-supplied histogram leaves no pass over the data: the separate kernel computes the same checksum
+    dev = [H.to_dev(h) for h in host]
+    hist = torch.from_numpy(np.stack([np.bincount(h, minlength=256) for h in host]).astype(np.int32)).cuda()
+    _kernels_run()
+    m2, sz2 = H.ours_ans_encode(dev, 10, checksum=True, histogram=hist)
+    assert "k_checksum" in _kernels_run()
+    for i, h in enumerate(host):
+        assert np.array_equal(H.row_bytes(m2, i, sz2[i]), oracle.ans_encode(h, 10, use_checksum=True, hist=np.bincount(h, minlength=256).astype(np.uint32)))
