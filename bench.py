@@ -609,9 +609,14 @@ def run_collectives(dist, rank, world):
     sys.path.insert(0, os.path.join(ROOT, "scripts"))
     import bench_collectives
     try:
-        return bench_collectives.measure(dist, rank, world, mib=64, steps=10, warmup=3, chunks=1)
+        res = bench_collectives.measure(dist, rank, world, mib=64, steps=10, warmup=3, chunks=1)
     except Exception as e:  # the sharded line must not be lost to a collective failure; say what happened
-        return {"error": f"{type(e).__name__}: {e}"}
+        res = {"error": f"{type(e).__name__}: {e}"}
+    try:  # BASELINE configs[2](ii): one fp32 64 x 16 MiB batch partitioned over the ranks
+        res["sharded_fp32"] = bench_collectives.measure_sharded(dist, rank, world)
+    except Exception as e:
+        res["sharded_fp32"] = {"error": f"{type(e).__name__}: {e}"}
+    return res
 
 
 def reference_cpu_arm(args):

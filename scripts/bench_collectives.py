@@ -119,6 +119,47 @@ def measure(dist_mod, rank, world, mib=64, steps=10, warmup=3, chunks=1, peer=Tr
     return res
 
 
+def measure_sharded(dist_mod, rank, world, batch=64, words=4 << 20, steps=10, warmup=3):
+    """BASELINE configs[2](ii): one fp32 batch of 64 x 16 MiB whose elements are partitioned over the ranks by index
+    (dist.partition / compress_sharded; no data-path collective). Every rank compresses and decompresses its slice;
+    the job's throughput is the whole batch's uncompressed bytes over the slowest rank's time (strong scaling: the
+    total work is fixed). The round trip of every element is checked."""
+    from dietgpu_fork_b200 import codec
+    lo, hi = dgd.partition(batch, world, rank)
+    g = torch.Generator(device="cuda").manual_seed(3000)
+    ins = []
+    for i in range(batch):  # the same batch on every rank; only the own slice is kept
+        t = torch.randn(words, device="cuda", generator=g)
+        if lo <= i < hi:
+            ins.append(t)
+    n = hi - lo
+    mx = (codec.get_max_float_compressed_size(codec.FLOAT32, words) + 15) // 16 * 16
+    comp = torch.empty((max(n, 1), mx), dtype=torch.uint8, device="cuda")
+    rows = [comp[i] for i in range(n)]
+    sizes = torch.zeros(max(n, 1), dtype=torch.int32, device="cuda")
+    outs = [torch.empty_like(t) for t in ins]
+    ok = torch.zeros(max(n, 1), dtype=torch.uint8, device="cuda")
+    temp = torch.empty(int(2.5 * n * words * 4) + (64 << 20), dtype=torch.uint8, device="cuda")
+
+    def comp_fn():
+        if n:
+            codec.float_compress(codec.FLOAT32, ins, rows, sizes, 10, False, temp=temp)
+
+    def dec_fn():
+        if n:
+            codec.float_decompress(codec.FLOAT32, rows, outs, ok, None, 10, False, temp=temp)
+
+    t_c = timed(comp_fn, steps, warmup)
+    t_d = timed(dec_fn, steps, warmup)
+    for a, b in zip(ins, outs):
+        assert torch.equal(a.view(torch.int32), b.view(torch.int32)), "sharded round trip mismatch"
+    U = batch * words * 4
+    return {"workload": f"fp32 N(0, 1), one batch of {batch} x {words * 4 >> 20} MiB partitioned over {world} GPUs by element",
+            "scaling": "strong", "elements_per_rank": n, "compress_ms": round(t_c, 4), "decompress_ms": round(t_d, 4),
+            "compress_GBps": round(U / t_c / 1e6, 1), "decompress_GBps": round(U / t_d / 1e6, 1),
+            "round_trip_GBps": round(2 * U / (t_c + t_d) / 1e6, 1)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mib", type=int, default=64)
@@ -131,6 +172,7 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
     dist.init_process_group("nccl")
     res = measure(dist, rank, world, a.mib, a.steps, a.warmup, a.chunks, bool(a.peer))
+    res["sharded_fp32"] = measure_sharded(dist, rank, world, steps=a.steps, warmup=a.warmup)
     if rank == 0:
         print(json.dumps(res), flush=True)
     dist.destroy_process_group()

@@ -49,6 +49,69 @@ def timed(fn, steps, warmup=3):
     return a.elapsed_time(b) / steps
 
 
+CPU_SAMPLE = 0  # set by --cpu-sample: batch elements of every config also timed on the host cores with the CPU oracle
+
+
+def cpu_model():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def cpu_baseline(kind, ft, ins, counts, sparse):
+    """The CPU oracle (oracle/, a restatement of the same stream formats; the reference has no CPU codec) on a
+    bounded sample of this config: the first CPU_SAMPLE elements, each cut to at most 4 Mi symbols / words."""
+    import time
+
+    import oracle
+    k = min(len(ins), CPU_SAMPLE)
+    cap = 4 << 20
+    wdt = np.uint8 if kind == "ans" else oracle.WORD_DTYPE[ft]
+    host = [ins[i].view(torch.uint8).reshape(-1)[: min(counts[i], cap) * (1 if kind == "ans" else wdt().itemsize)]
+            .cpu().numpy().view(wdt).copy() for i in range(k)]
+    nbytes = sum(h.nbytes for h in host)
+    threads = oracle.num_threads()
+    if not sparse:  # untimed warm-up: thread pool start, page faults of the library
+        w = host[0][:65536]
+        if kind == "ans":
+            oracle.ans_encode_batch([w] * threads, [np.zeros(oracle.ans_max_compressed_size(w.size), np.uint8) for _ in range(threads)])
+        else:
+            oracle.float_compress_batch(ft, [w] * threads,
+                                        [np.zeros(oracle.float_max_compressed_size(ft, w.size), np.uint8) for _ in range(threads)])
+    t0 = time.perf_counter()
+    if kind == "ans":
+        comp = [np.zeros(oracle.ans_max_compressed_size(h.size), np.uint8) for h in host]
+        outs = [np.zeros(h.size, np.uint8) for h in host]
+        t0 = time.perf_counter()
+        oracle.ans_encode_batch(host, comp)
+        t1 = time.perf_counter()
+        oracle.ans_decode_batch(comp, outs)
+        t2 = time.perf_counter()
+    elif sparse:  # no batched driver for the sparse path: one element after the other, one thread
+        threads = 1
+        t0 = time.perf_counter()
+        comp = [oracle.sparse_float_compress(ft, h) for h in host]
+        t1 = time.perf_counter()
+        outs = [oracle.sparse_float_decompress(ft, c)[2] for c in comp]
+        t2 = time.perf_counter()
+    else:
+        comp = [np.zeros(oracle.float_max_compressed_size(ft, h.size), np.uint8) for h in host]
+        outs = [np.zeros(h.size, wdt) for h in host]
+        t0 = time.perf_counter()
+        oracle.float_compress_batch(ft, host, comp)
+        t1 = time.perf_counter()
+        oracle.float_decompress_batch(comp, outs)
+        t2 = time.perf_counter()
+    assert all(np.array_equal(a, b) for a, b in zip(host, outs)), "CPU oracle round trip mismatch"
+    return {"kind": "port", "cores": threads, "cpu": cpu_model(),
+            "sample": f"{k} element(s) of <= 4 Mi symbols each ({nbytes >> 20} MiB)",
+            "compress_GBps": round(nbytes / (t1 - t0) / 1e9, 3), "decompress_GBps": round(nbytes / (t2 - t1) / 1e9, 3)}
+
+
 def run_config(name, kind, ft, ins, counts, steps, sparse=False):
     """kind: 'ans' (bytes) or 'float'. ins: device tensors; counts: bytes (ans) or words (float)."""
     n = len(ins)
@@ -145,6 +208,8 @@ def run_config(name, kind, ft, ins, counts, steps, sparse=False):
         res["speedup"] = {"compress": round(rtc / tc, 3), "decompress": round(rtd / td, 3),
                           "round_trip": round((rtc + rtd) / (tc + td), 3)}
         del rt
+    if CPU_SAMPLE:
+        res["cpu_baseline"] = cpu_baseline(kind, ft, ins, counts, sparse)
     print(json.dumps(res), flush=True)
     del temp, comp, outs
     torch.cuda.empty_cache()
@@ -155,7 +220,11 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--only", default="")
     ap.add_argument("--custom", default="", help="comma list of bf16:<batch>:<KiB per element> (e.g. bf16:32:2048)")
+    ap.add_argument("--cpu-sample", type=int, default=0,
+                    help="also time the CPU oracle on this many elements of every config (bounded: <= 4 Mi symbols each)")
     a = ap.parse_args()
+    global CPU_SAMPLE
+    CPU_SAMPLE = a.cpu_sample
     only = set(a.only.split(",")) if a.only else None
     torch.cuda.set_device(0)
 
