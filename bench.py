@@ -572,6 +572,9 @@ def run_e2e(args, ins, ref, comp, rows, sizes, ok, dsizes, temp, dist, n_ranks):
             vals.append(n_ranks * 2.0 * U / (ms / steps * 1e-3) / 1e9)
         return float(np.median(vals)), vals
 
+    if dist is not None:  # all ranks measure at the same time: they share the host's memory system
+        torch.cuda.synchronize()
+        dist.barrier()
     link = pcie_duplex_gbs()
     if dist is not None:  # the slowest rank's link bounds the job
         t = torch.tensor([link], device="cuda", dtype=torch.float64)
