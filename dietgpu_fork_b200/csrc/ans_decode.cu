@@ -41,6 +41,10 @@ __global__ void __launch_bounds__(256) k_decodePrep(const DecodeArgs a, DecInfo*
   __shared__ uint32_t sCdf[257];
   __shared__ uint32_t sWarp[8];
   const uint32_t e = blockIdx.x, plane = blockIdx.y, s = threadIdx.x, lane = s & 31, w = s >> 5;
+  // programmatic dependent launch: k_decode (launched with the stream-serialization attribute) may become resident
+  // and run its prologue now; it waits (griddepcontrol.wait) for this grid to complete before it reads anything
+  // written here. Without the attribute on the next launch this is a no-op.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (e == 0 && plane == 0 && s == 0) *tileCounter = 0; // k_decode's dynamic tile claims start here
   const Elem el = a.elems[e];
   const uint8_t* arch = (const uint8_t*)el.in;
@@ -468,6 +472,9 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 4 : 6) k_decode
   const uint32_t geMask = laneMaskGe();
   const DecodeArgs& a = p.a;
 
+  // everything above touched only this CTA's shared memory; what k_decodePrep wrote (info, LUTs, the claim counter)
+  // is read from here on (no-op unless this grid was launched as a programmatic dependent)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   // Tiles are claimed in order, `claimTiles` at a time (first claim static), so the CTAs finish together.
   __shared__ uint32_t sNext;
   uint32_t cur = 0xffffffffu;
@@ -651,7 +658,25 @@ static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
   ctas = min(ctas, divUp(p.a.totalTiles, p.claimTiles));
   {
     ProfScope ps__("k_decode", s);
-    k_decode<PB, FT><<<ctas, kDecWarps * 32, smemBytes, s>>>(p);
+    // Programmatic dependent launch: this grid becomes resident during k_decodePrep and runs its prologue; it waits
+    // (griddepcontrol.wait) before it reads what the prep kernel wrote. Measured on B200 (same box, DGB_DEC_PDL 0 / 1):
+    // bf16 128 x 4 MiB decompress 0.2719 -> 0.2697 ms, 16 x 8 MiB 0.0843 -> 0.0808; but at one wave of tiles it costs:
+    // 1 x 64 MiB 0.058 -> 0.068 ms, 32 x 2 MiB 0.061 -> 0.072. So: from two waves up.
+    if (DGB_KNOB("DGB_DEC_PDL", 1) != 0 && p.a.totalTiles >= 2048) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(ctas);
+      cfg.blockDim = dim3(kDecWarps * 32);
+      cfg.dynamicSmemBytes = smemBytes;
+      cfg.stream = s;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      DGB_CUDA(cudaLaunchKernelEx(&cfg, k_decode<PB, FT>, p));
+    } else {
+      k_decode<PB, FT><<<ctas, kDecWarps * 32, smemBytes, s>>>(p);
+    }
   }
   DGB_CUDA(cudaGetLastError());
   return kOk;
