@@ -40,7 +40,7 @@ __device__ __forceinline__ uint32_t ballotToBitmap(uint32_t b) { return __byte_p
 __device__ __forceinline__ uint32_t bitmapToBallot(uint32_t w) { return __brev(__byte_perm(w, 0, 0x0123)); }
 
 template <typename Word>
-__global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
+__global__ void __launch_bounds__(256, sizeof(Word) == 8 ? 2 : 4) k_sparseCompact(const SparseParams p) {
   __shared__ uint32_t sTicket, sElem, sExcl;
   __shared__ uint32_t sWarpTot[8];
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -84,31 +84,72 @@ __global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
     uint32_t* bitmap = (uint32_t*)(out + 16);
     Word* dense = (Word*)p.dense + el.planeOff;
 
-    // ---- load 32 steps of 32 words, one ballot per step ----
-    // (keeping only the ballots and reading the non-zero words again later halves the registers and doubles the
-    // resident warps, but measured slower: 0.267 vs 0.242 ms for 16 x 16 MiB at 90 % zeros)
+    // Reference quirk (GpuSparseFloatCompress.cuh:163-183): the last word goes to idx[N-2] + 1 and
+    // nnz = idx[N-2] + bitmap[N-1] + 1, i.e. word N-2 is assumed non-zero. When it is zero the
+    // dense array has one extra slot (never written by the reference; 0 here) before the last word.
+    const bool quirk = n >= 2 && in[n - 2] == Word(0);
+
+    // ---- phase A: this warp's 1024 words -> 32 ballots (lane k keeps the ballot of words [32k, 32k + 32)) ----
+    // Full, 16-byte aligned warp blocks (all but an element's last block and misaligned inputs) load 16 bytes per
+    // lane and step - W consecutive words - and keep them in registers; the W-bit masks of the 32 / W lanes that
+    // share a 32-word group are OR-ed together with shuffles. (ncu, round 2: with one word per lane and step the
+    // kernel was instruction bound, 34 warp instructions per 32 words at 46 % issue activity; this path needs
+    // about 10.) Other blocks take one word per lane and step and keep only the ballots: their non-zeros are read
+    // again in phase B.
+    constexpr uint32_t W = 16 / sizeof(Word);       // words per lane and step
+    constexpr uint32_t S = kSpWarpWords / (32 * W); // steps per warp block
+    constexpr uint32_t LPG = 32 / W;                // lanes that share a 32-word group
     const uint32_t wbase = t * kSpTileWords + w * kSpWarpWords;
-    Word v[kSpSteps];
+    const bool fast = (((uintptr_t)in) & 15u) == 0 && wbase + kSpWarpWords <= n && !(quirk && wbase + kSpWarpWords == n);
+    // (ncu on this version, profiles/r2_k_sparseCompact_v2.txt: 54 M instead of 71 M instructions, but 46 % of the
+    // samples now sit at the barrier behind the tile-offset look-up and issue activity is 34 %: in a persistent grid
+    // every tile waits for the slowest load among its predecessors. Not keeping the vectors across that wait -
+    // reloading the ones with a non-zero in phase B, 32 registers, 8 CTAs per SM - was slower, 0.151 vs 0.135 ms: the
+    // eight loads in flight per thread then spill. An aggregate-only offset scheme without any chain was no faster
+    // than the look-back either, 0.156 ms.)
+    const uint4* v4 = (const uint4*)(in + wbase);
+    uint4 x[S];
+    uint32_t myBallot = 0;
+    if (fast) {
 #pragma unroll
-    for (uint32_t k = 0; k < kSpSteps; ++k) {
-      uint32_t i = wbase + k * 32 + lane;
-      v[k] = i < n ? in[i] : Word(0);
-    }
-    uint32_t myBallot = 0; // lane k keeps the ballot of step k
+      for (uint32_t s0 = 0; s0 < S; ++s0) x[s0] = __ldg(v4 + s0 * 32 + lane);
 #pragma unroll
-    for (uint32_t k = 0; k < kSpSteps; ++k) {
-      uint32_t b = __ballot_sync(0xffffffffu, v[k] != Word(0));
-      if (lane == k) myBallot = b;
+      for (uint32_t s0 = 0; s0 < S; ++s0) {
+        uint32_t m; // bit j: word j of this lane's vector is non-zero
+        if constexpr (sizeof(Word) == 4) {
+          m = (x[s0].x != 0) | ((x[s0].y != 0) << 1) | ((x[s0].z != 0) << 2) | ((x[s0].w != 0) << 3);
+        } else if constexpr (sizeof(Word) == 2) {
+          m = ((x[s0].x & 0xffffu) != 0) | (((x[s0].x >> 16) != 0) << 1) | (((x[s0].y & 0xffffu) != 0) << 2) |
+              (((x[s0].y >> 16) != 0) << 3) | (((x[s0].z & 0xffffu) != 0) << 4) | (((x[s0].z >> 16) != 0) << 5) |
+              (((x[s0].w & 0xffffu) != 0) << 6) | (((x[s0].w >> 16) != 0) << 7);
+        } else {
+          m = ((x[s0].x | x[s0].y) != 0) | (((x[s0].z | x[s0].w) != 0) << 1);
+        }
+        uint32_t b = m << ((lane % LPG) * W); // in its place inside the group's ballot
+#pragma unroll
+        for (uint32_t o = 1; o < LPG; o <<= 1) b |= __shfl_xor_sync(0xffffffffu, b, o);
+        // this step holds groups [s0 * W, s0 * W + W); lane k of that range takes group k's ballot from its first lane
+        const uint32_t got = __shfl_sync(0xffffffffu, b, (lane % W) * LPG);
+        if (lane / W == s0) myBallot = got;
+      }
+    } else {
+#pragma unroll 4
+      for (uint32_t k = 0; k < kSpSteps; ++k) {
+        const uint32_t i = wbase + k * 32 + lane;
+        const Word val = i < n ? in[i] : Word(0);
+        const uint32_t b = __ballot_sync(0xffffffffu, val != Word(0));
+        if (lane == k) myBallot = b;
+      }
     }
     const uint32_t myCount = __popc(myBallot);
-    uint32_t inc = myCount; // inclusive scan over steps
+    uint32_t inc = myCount; // inclusive scan over the 32 groups
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= (uint32_t)o) inc += x;
+      uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= (uint32_t)o) inc += y;
     }
     if (lane == 31) sWarpTot[w] = inc;
-    // bitmap words of this warp: step k covers words [wbase + 32k, +32) -> bitmap u32 index (wbase/32 + k)
+    // bitmap words of this warp: group k covers words [wbase + 32k, +32) -> bitmap u32 index (wbase/32 + k)
     {
       uint32_t stepWord = wbase + lane * 32;
       if (stepWord < roundUp(n, 32)) bitmap[stepWord >> 5] = ballotToBitmap(myBallot);
@@ -117,9 +158,9 @@ __global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
     uint32_t warpOff = 0, tileTot = 0;
 #pragma unroll
     for (uint32_t j = 0; j < 8; ++j) {
-      uint32_t x = sWarpTot[j];
-      warpOff += j < w ? x : 0u;
-      tileTot += x;
+      uint32_t y = sWarpTot[j];
+      warpOff += j < w ? y : 0u;
+      tileTot += y;
     }
     if (w == 0) {
       uint32_t ex = lookbackExclusive(p.tileState + el.tileBase, t, tileTot, p.errFlag);
@@ -127,21 +168,45 @@ __global__ void __launch_bounds__(256) k_sparseCompact(const SparseParams p) {
     }
     __syncthreads();
     const uint32_t excl = sExcl;
-    const uint32_t stepOff = excl + warpOff + inc - myCount; // lane k: where step k's non-zeros start
-    // Reference quirk (GpuSparseFloatCompress.cuh:163-183): the last word goes to idx[N-2] + 1 and
-    // nnz = idx[N-2] + bitmap[N-1] + 1, i.e. word N-2 is assumed non-zero. When it is zero the
-    // dense array has one extra slot (never written by the reference; 0 here) before the last word.
-    const bool quirk = n >= 2 && in[n - 2] == Word(0);
+    const uint32_t stepOff = excl + warpOff + inc - myCount; // lane k: where group k's non-zeros start
+
+    // ---- phase B: the non-zeros go to their dense positions ----
+    if (fast) {
 #pragma unroll
-    for (uint32_t k = 0; k < kSpSteps; ++k) {
-      uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
-      uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
-      uint32_t dst = o + __popc(b & ltMask);
-      if (quirk && wbase + k * 32 + lane == n - 1) {
-        dense[dst] = Word(0);
-        dst += 1;
+      for (uint32_t s0 = 0; s0 < S; ++s0) {
+        const uint32_t g = s0 * W + lane / LPG, off = (lane % LPG) * W; // this lane's group and first bit in it
+        const uint32_t b = __shfl_sync(0xffffffffu, myBallot, g);
+        uint32_t dst = __shfl_sync(0xffffffffu, stepOff, g) + __popc(b & ((1u << off) - 1u));
+        const uint32_t m = (b >> off) & ((1u << W) - 1u);
+        const uint4 xs = x[s0];
+        Word vals[W];
+        if constexpr (sizeof(Word) == 4) {
+          vals[0] = xs.x; vals[1] = xs.y; vals[2] = xs.z; vals[3] = xs.w;
+        } else if constexpr (sizeof(Word) == 2) {
+          vals[0] = (Word)xs.x; vals[1] = (Word)(xs.x >> 16); vals[2] = (Word)xs.y; vals[3] = (Word)(xs.y >> 16);
+          vals[4] = (Word)xs.z; vals[5] = (Word)(xs.z >> 16); vals[6] = (Word)xs.w; vals[7] = (Word)(xs.w >> 16);
+        } else {
+          vals[0] = (Word)xs.x | ((Word)xs.y << 32);
+          vals[1] = (Word)xs.z | ((Word)xs.w << 32);
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < W; ++j) {
+          if ((m >> j) & 1u) dense[dst++] = vals[j];
+        }
       }
-      if ((b >> lane) & 1u) dense[dst] = v[k];
+    } else {
+#pragma unroll 4
+      for (uint32_t k = 0; k < kSpSteps; ++k) {
+        const uint32_t b = __shfl_sync(0xffffffffu, myBallot, k);
+        const uint32_t o = __shfl_sync(0xffffffffu, stepOff, k);
+        const uint32_t i = wbase + k * 32 + lane;
+        uint32_t dst = o + __popc(b & ltMask);
+        if (quirk && i == n - 1) {
+          dense[dst] = Word(0);
+          dst += 1;
+        }
+        if ((b >> lane) & 1u) dense[dst] = in[i];
+      }
     }
     if (t == 0 && tid == 0) ((uint4*)out)[0] = make_uint4(n, 0u, 0u, 0u); // GpuSparseFloatHeader
     if (t == numTiles - 1) {
