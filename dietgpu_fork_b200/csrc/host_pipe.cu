@@ -282,6 +282,35 @@ int compressHost(int ft, int pb, int useChecksum, uint32_t num, const void* cons
   return rc ? rc : rcSync ? rcSync : status;
 }
 
+// Length an archive in HOST memory claims for itself (headers only; dietgpu/ans/GpuANSUtils.cuh:68-86,
+// dietgpu/float/GpuFloatUtils.cuh:19-96), or 0 when a header it needs lies beyond `avail` bytes or is not sane. The
+// device decoder trusts the header's word count for the extent of what it reads, so a caller-visible size is checked
+// against it here, before anything is copied (a wrong magic is left to the decoder, which reports success = 0).
+static uint64_t claimedArchiveBytes(int ft, const void* archive, uint64_t avail) {
+  const uint8_t* a = (const uint8_t*)archive;
+  uint64_t off = 0;
+  if (ft != kFtNone) {
+    if (avail < kFloatHeaderBytes) return 0;
+    uint32_t h[5];
+    memcpy(h, a, sizeof(h));
+    if (h[0] != kFloatMagic || (int)(h[2] & 0xfu) != ft) return avail; // not ours to size: the decoder rejects it
+    off = (uint64_t)kFloatHeaderBytes + floatRawBytes(ft, h[1]);
+    if (ft == kFtF64) {
+      if (off + kAnsHeaderBytes > avail) return 0;
+      uint32_t ah[4];
+      memcpy(ah, a + off, sizeof(ah));
+      if (ah[0] != kAnsMagic) return avail;
+      if (h[4] != (uint64_t)ansOverhead(ah[1]) + 2ull * ah[3]) return 0; // firstCompSegmentBytes must be that archive's length
+      off += h[4];
+    }
+  }
+  if (off + kAnsHeaderBytes > avail) return 0;
+  uint32_t ah[4];
+  memcpy(ah, a + off, sizeof(ah));
+  if (ah[0] != kAnsMagic) return avail;
+  return off + ansOverhead(ah[1]) + 2ull * ah[3];
+}
+
 int decompressHost(int ft, int pb, int useChecksum, uint32_t num, const void* const* in, const uint32_t* inBytesArg,
                    void* const* out, const uint32_t* outCapacity, uint8_t* outSuccess, uint32_t* outSize,
                    cudaStream_t user) {
@@ -293,6 +322,12 @@ int decompressHost(int ft, int pb, int useChecksum, uint32_t num, const void* co
   std::vector<size_t> inBytes(num), outBytes(num);
   for (uint32_t i = 0; i < num; ++i) {
     if (inBytesArg[i] < (ft == kFtNone ? kAnsHeaderBytes : kFloatHeaderBytes)) return kErrInvalidArg;
+    const uint64_t claimed = claimedArchiveBytes(ft, in[i], inBytesArg[i]);
+    if (claimed == 0 || claimed > inBytesArg[i]) {
+      fprintf(stderr, "dietgpu_b200: host-buffer decode: archive %u claims %llu bytes but in_bytes is %u\n", i,
+              (unsigned long long)claimed, inBytesArg[i]);
+      return kErrInvalidArg;
+    }
     inBytes[i] = inBytesArg[i];
     outBytes[i] = (size_t)outCapacity[i] * ub;
   }

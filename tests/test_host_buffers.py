@@ -104,3 +104,24 @@ def test_host_decompress_capacity_too_small_reports_failure():
     ok, _ = codec.float_decompress_host(BF16, [hout], [csz], [dec], out_capacity=[100])
     assert ok == [0]
     codec.host_release()
+
+
+def test_host_decompress_rejects_archives_longer_than_in_bytes():
+    """in_bytes is the caller's statement of how much archive there is: headers that claim more (a truncated buffer,
+    a corrupted word count) are refused on the host before anything is copied or decoded."""
+    from dietgpu_fork_b200 import _capi
+    n = 50000
+    host = torch.from_numpy(datagen.float_words(2, n, seed=9).view(np.int16).copy()).view(torch.bfloat16)
+    comp = torch.zeros(codec.get_max_float_compressed_size(2, n), dtype=torch.uint8)
+    size = codec.float_compress_host(2, [host], [comp])[0]
+    out = torch.zeros(n, dtype=torch.bfloat16)
+    ok, _ = codec.float_decompress_host(2, [comp], [size], [out])  # exact size: fine
+    assert ok == [1] and torch.equal(out.view(torch.int16), host.view(torch.int16))
+    with pytest.raises(_capi.DietGpuError):
+        codec.float_decompress_host(2, [comp], [size - 16], [out])  # truncated buffer
+    bad = comp.clone()
+    ans_off = 32 + (n + 15) // 16 * 16
+    bad[ans_off + 12:ans_off + 16] = torch.tensor([0xFF, 0xFF, 0xFF, 0x0F], dtype=torch.uint8)  # totalCompressedWords
+    with pytest.raises(_capi.DietGpuError):
+        codec.float_decompress_host(2, [bad], [size], [out])
+
