@@ -297,6 +297,23 @@ __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
 }
 
 // ---------------------------------------------------------------------------------------------
+#ifdef DGB_TRACE_ELEMS
+// Debugging aid (make EXTRA=-DDGB_TRACE_ELEMS, never in the shipped build): per element of the fused kernel's last
+// launch {ready, ~first run start, last block end, ~first compaction start, last compaction end, summed wait ns}
+// in globaltimer ns; the "first" slots hold the complement so that one zero-initialised atomicMax serves all.
+static __device__ unsigned long long g_elemTrace[6 * 1024];
+__device__ __forceinline__ unsigned long long traceNow() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define DGB_TRACE_MAX(e, k) do { if ((e) < 1024u) atomicMax(&g_elemTrace[6 * (e) + (k)], traceNow()); } while (0)
+#define DGB_TRACE_MIN(e, k) do { if ((e) < 1024u) atomicMax(&g_elemTrace[6 * (e) + (k)], ~traceNow()); } while (0)
+#else
+#define DGB_TRACE_MAX(e, k) do { } while (0)
+#define DGB_TRACE_MIN(e, k) do { } while (0)
+#endif
+
 // Warp-level encoder. Work unit = run of 8 >> runShift consecutive blocks of one element (half of an
 // 8-block tile for large batches): one element lookup and one uninterrupted symbol stream per run.
 //   symbols: one byte load per lane and symbol row straight from global memory, requested 8 rows
@@ -354,12 +371,18 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     w.elemSrc = a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in;
     if (FUSED) {
       if (lane == 0) { // relaxed polling with growing back-off (an acquire load per poll would flush L1 each time)
+#ifdef DGB_TRACE_ELEMS
+        const unsigned long long tw0 = traceNow();
+#endif
         uint32_t ns = 200;
         while (ldRelaxed(p.ready + w.curElem) == 0) {
           __nanosleep(ns);
           if (ns < 3200) ns *= 2;
         }
         (void)ldAcquire(p.ready + w.curElem);
+#ifdef DGB_TRACE_ELEMS
+        if (w.curElem < 1024u) atomicAdd(&g_elemTrace[6 * w.curElem + 5], traceNow() - tw0);
+#endif
       }
       __syncwarp();
     }
@@ -381,6 +404,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
   }
   uint32_t blk = (tile - w.tileBase) * kTileBlocks + (run & ((1u << p.runShift) - 1u)) * runBlocks;
   if (blk >= w.nb) return; // empty element, or the device-side size is smaller than the host bound
+  if (FUSED && lane == 0) DGB_TRACE_MIN(w.curElem, 1);
   const uint32_t n = w.n;
   const uint32_t runSyms = min(n, (blk + runBlocks) * kBlockSyms) - blk * kBlockSyms;
   const uint8_t* src = w.elemSrc + (size_t)blk * kBlockSyms;
@@ -412,6 +436,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
       if (lane == 0) {
         p.blockWords[gb] = words;
         if (FUSED) {
+          DGB_TRACE_MAX(w.curElem, 2);
           // sizes and, in the high bits, the number of finished blocks (release: slot and size first); the
           // in-kernel compaction of a tile starts as soon as these counts say its predecessors are encoded
           redRelease(&w.groupSum[blk / kGroupBlocks], paddedWords + kGroupCountOne);
@@ -539,6 +564,7 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
   const uint32_t nb = divUp(n, kBlockSyms);
   const uint32_t numTiles = max(1u, divUp(nb, kTileBlocks));
   if (t >= numTiles) return;
+  if (lane == 0) DGB_TRACE_MIN(e, 3);
   uint8_t* ans = (uint8_t*)el.out;
   uint8_t* fbase = nullptr;
   if (a.floatType != kFtNone) {
@@ -609,6 +635,7 @@ static __device__ __noinline__ void coalesceTileWarp(const EncParams& p, int pro
     fill += nv;
   }
   if (fill) drain();
+  if (lane == 0) DGB_TRACE_MAX(e, 4);
 
   if (t == 0) { // pdf table; zero for absent symbols and for an empty element
     const uint2* tab = p.table + (size_t)e * 256;

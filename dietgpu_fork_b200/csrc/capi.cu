@@ -606,7 +606,7 @@ using namespace dgb;
 
 extern "C" {
 
-const char* dgb_version(void) { return "dietgpu_b200 r1 sm_100a"; }
+const char* dgb_version(void) { return "dietgpu_b200 r2 sm_100a"; }
 
 size_t dgb_last_temp_bytes_used(void) { return Temp::lastHighWater(); }
 

@@ -26,6 +26,7 @@
 // co-resident.
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #include "ans_encode.cuh"
@@ -188,7 +189,10 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
                                         p.ep.table + (size_t)accElem * 256, normSm);
         __threadfence();
         __syncthreads();
-        if (tid == 0) stRelease(p.ready + accElem, 1u);
+        if (tid == 0) {
+          DGB_TRACE_MAX(accElem, 0);
+          stRelease(p.ready + accElem, 1u);
+        }
       }
       __syncthreads(); // sBcast is rewritten after this point
       accSlices = 0;
@@ -360,6 +364,13 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   static const char* tracePath = getenv("DGB_FUSED_TRACE"); // debugging aid: per-CTA timeline of the last launch
   p.trace = nullptr;
   if (tracePath) DGB_CUDA(cudaMalloc(&p.trace, 6ull * 8 * grid));
+#ifdef DGB_TRACE_ELEMS
+  {
+    void* et = nullptr;
+    DGB_CUDA(cudaGetSymbolAddress(&et, g_elemTrace));
+    DGB_CUDA(cudaMemsetAsync(et, 0, sizeof(unsigned long long) * 6 * 1024, s));
+  }
+#endif
   {
     ProfScope ps__("k_compressFused", s);
     kern<<<grid, kFusedThreads, kFusedSmem, s>>>(p);
@@ -376,6 +387,16 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
                 h[6 * i + 5]);
       fclose(f);
     }
+#ifdef DGB_TRACE_ELEMS
+    std::vector<unsigned long long> he(6 * 1024);
+    DGB_CUDA(cudaMemcpyFromSymbol(he.data(), g_elemTrace, he.size() * 8));
+    if (FILE* f = fopen((std::string(tracePath) + ".elems").c_str(), "w")) {
+      for (uint32_t e = 0; e < p.sp.numElems && e < 1024u; ++e)
+        fprintf(f, "%u %llu %llu %llu %llu %llu %llu\n", e, he[6 * e], ~he[6 * e + 1], he[6 * e + 2], ~he[6 * e + 3],
+                he[6 * e + 4], he[6 * e + 5]);
+      fclose(f);
+    }
+#endif
   }
   return kOk;
 }

@@ -241,7 +241,7 @@ void dgb_profile_enable(int on);
  * records; returns the number of distinct kernels. */
 int dgb_profile_report(char* buf, size_t cap);
 
-/* library version / build tag, e.g. "dietgpu_b200 r1 sm_100a" */
+/* library version / build tag, e.g. "dietgpu_b200 r2 sm_100a" */
 const char* dgb_version(void);
 
 #ifdef __cplusplus
