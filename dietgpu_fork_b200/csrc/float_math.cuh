@@ -39,8 +39,11 @@ __device__ __forceinline__ RawSections rawSections(int ft, uint8_t* rawBase, uin
 }
 
 // per-halfword rotate-left-by-one of two packed 16-bit words
+// one bit-select LOP3 ((a & m) | (b & ~m)) instead of two ANDs with different immediates and an OR
 __device__ __forceinline__ uint32_t rotl1x2(uint32_t x) {
-  return ((x << 1) & 0xfffefffeu) | ((x >> 15) & 0x00010001u);
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, 0xfffefffe, 0xE4;" : "=r"(r) : "r"(x << 1), "r"(x >> 15));
+  return r;
 }
 __device__ __forceinline__ uint32_t rotr1x2(uint32_t y) {
   return ((y >> 1) & 0x7fff7fffu) | ((y << 15) & 0x80008000u);

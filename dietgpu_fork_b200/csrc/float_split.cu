@@ -13,7 +13,8 @@ template <int FT, bool PIPE>
 __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
   constexpr int kPlanes = FloatTraits<FT>::kPlanes;
   constexpr uint32_t kHistWords = splitHistWords<256>();
-  extern __shared__ __align__(16) uint32_t sh[]; // kPlanes * kHistWords
+  extern __shared__ __align__(16) uint8_t smemRaw[]; // kSplitHistAlign + kPlanes * kHistWords * 4
+  uint32_t* const sh = (uint32_t*)splitHistBase(smemRaw);
   const uint32_t tid = threadIdx.x;
   for (uint32_t i = tid; i < kPlanes * kHistWords; i += 256) sh[i] = 0;
   __syncthreads();
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(256) k_floatSplit(const SplitParams p) {
 
 template <int FT>
 static int launchSplitT(SplitParams& p, cudaStream_t s) {
-  constexpr uint32_t smemBytes = FloatTraits<FT>::kPlanes * splitHistWords<256>() * 4;
+  constexpr uint32_t smemBytes = kSplitHistAlign + FloatTraits<FT>::kPlanes * splitHistWords<256>() * 4;
   const bool pipe = DGB_KNOB("DGB_SPLIT_PIPE", 1) != 0; // experiment knob
   auto kern = pipe ? k_floatSplit<FT, true> : k_floatSplit<FT, false>;
   {

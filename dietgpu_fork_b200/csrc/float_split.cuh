@@ -48,8 +48,27 @@ struct SplitParams {
   int normProbBits;
 };
 
-__device__ __forceinline__ void splitHistAdd(uint32_t* wh, uint32_t sym, uint32_t rep) {
-  atomicAdd(&wh[sym * kSplitRep + rep], 1u);
+// The CTA's bins start at a 4096-byte aligned SHARED address (splitHistBase): a warp's 256 x kSplitRep counters are
+// 4 KB, so a counter's address is  warp base | symbol << 4 | replica << 2  and an increment costs a shift, one LOP3
+// and the ATOMS (an index the compiler has to add to a base costs one instruction more per symbol).
+constexpr uint32_t kSplitHistAlign = 256 * kSplitRep * 4; // 4096
+static_assert(kSplitHistAlign == 4096, "one warp's bins = address bits 2..11");
+// first kSplitHistAlign-aligned byte of a dynamic shared-memory block (callers allocate kSplitHistAlign more)
+__device__ __forceinline__ uint8_t* splitHistBase(uint8_t* smem) {
+  const uint32_t a = smemAddr(smem);
+  return smem + ((kSplitHistAlign - (a & (kSplitHistAlign - 1u))) & (kSplitHistAlign - 1u));
+}
+// whRep: shared address of the warp's bins | replica * 4; symShl4: the symbol at bits 4..11, anything elsewhere
+__device__ __forceinline__ void splitHistAddAt(uint32_t whRep, uint32_t symShl4) {
+  const uint32_t addr = (symShl4 & 0xff0u) | whRep;
+  asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+// the four bytes of x
+__device__ __forceinline__ void splitHistAdd4(uint32_t whRep, uint32_t x) {
+  splitHistAddAt(whRep, x << 4);
+  splitHistAddAt(whRep, x >> 4);
+  splitHistAddAt(whRep, x >> 12);
+  splitHistAddAt(whRep, x >> 20);
 }
 
 // sums the warps x replicas of the bins this thread owns, adds to global, clears. Callers bracket it with
@@ -74,28 +93,24 @@ __device__ __forceinline__ void splitHistFlush(uint32_t* sh, uint32_t* g, uint32
 }
 
 template <int FT, int G>
-__device__ __forceinline__ void splitHistGroup(uint32_t* wh0, uint32_t* wh1, const uint32_t* ex, const uint32_t* ex1,
-                                               uint32_t rep) {
+__device__ __forceinline__ void splitHistGroup(uint32_t wh0, uint32_t wh1, const uint32_t* ex, const uint32_t* ex1) {
   if constexpr (G == 8) {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      splitHistAdd(wh0, (ex[0] >> (8 * b)) & 0xffu, rep);
-      splitHistAdd(wh0, (ex[1] >> (8 * b)) & 0xffu, rep);
-    }
+    splitHistAdd4(wh0, ex[0]);
+    splitHistAdd4(wh0, ex[1]);
   } else if constexpr (G == 4) {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) splitHistAdd(wh0, (ex[0] >> (8 * b)) & 0xffu, rep);
+    splitHistAdd4(wh0, ex[0]);
   } else {
-    splitHistAdd(wh0, ex[0] & 0xffu, rep);
-    splitHistAdd(wh0, ex[0] >> 8, rep);
-    splitHistAdd(wh1, ex1[0] & 0xffu, rep);
-    splitHistAdd(wh1, ex1[0] >> 8, rep);
+    splitHistAddAt(wh0, ex[0] << 4);
+    splitHistAddAt(wh0, ex[0] >> 4);
+    splitHistAddAt(wh1, ex1[0] << 4);
+    splitHistAddAt(wh1, ex1[0] >> 4);
   }
 }
 
 // One tile of element e (el = elems[e], n = its word count) by the NT threads of the CTA, or the slice
 // [slice * sliceWords, (slice + 1) * sliceWords) of it (sliceWords: a power of two dividing the tile). sh: the
-// CTA's histogram bins (kPlanes * splitHistWords<NT>() words, zeroed by the caller).
+// CTA's histogram bins (kPlanes * splitHistWords<NT>() words at a kSplitHistAlign-aligned shared address, zeroed by
+// the caller).
 template <int FT, int NT, bool PIPE = true>
 __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, const Elem& el, uint32_t n, uint32_t tile,
                                           uint32_t* sh, uint32_t sliceWords = kTileSyms, uint32_t slice = 0,
@@ -105,9 +120,9 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
   constexpr uint32_t G = Tr::kGroup;
   constexpr int kPlanes = Tr::kPlanes;
   const uint32_t tid = threadIdx.x;
-  uint32_t* wh0 = sh + (tid >> 5) * 256 * kSplitRep;
-  uint32_t* wh1 = wh0 + splitHistWords<NT>();
-  const uint32_t rep = tid & (kSplitRep - 1);
+  // this warp's bins | this lane's replica (sh is kSplitHistAlign-aligned, see splitHistAddAt)
+  const uint32_t wh0 = smemAddr(sh) + (tid >> 5) * kSplitHistAlign + (tid & (kSplitRep - 1)) * 4u;
+  const uint32_t wh1 = wh0 + splitHistWords<NT>() * 4u;
   const uint32_t t = tile - el.tileBase;
   const uint32_t sliceOff = slice * sliceWords;
   const uint32_t off = t * kTileSyms + sliceOff;
@@ -145,7 +160,7 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
           uint32_t ex[2], ex1[2];
           if (covered) ckVec(ck, x[k], g0 + i + NT * k, covered);
           splitGroup<FT>(x[k], g0 + i + NT * k, plane0, plane1, rs, ex, ex1);
-          splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+          splitHistGroup<FT, G>(wh0, wh1, ex, ex1);
         }
       }
     }
@@ -173,9 +188,9 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
           ckVec(ck, x1, g0 + i + NT, covered);
         }
         splitGroup<FT>(x0, g0 + i, plane0, plane1, rs, ex, ex1);
-        splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+        splitHistGroup<FT, G>(wh0, wh1, ex, ex1);
         splitGroup<FT>(x1, g0 + i + NT, plane0, plane1, rs, ex, ex1);
-        splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+        splitHistGroup<FT, G>(wh0, wh1, ex, ex1);
         i = j;
         if (!more) break;
         x0 = y0;
@@ -187,7 +202,7 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
       const uint4 xv = v[i];
       if (covered) ckVec(ck, xv, g0 + i, covered);
       splitGroup<FT>(xv, g0 + i, plane0, plane1, rs, ex, ex1);
-      splitHistGroup<FT, G>(wh0, wh1, ex, ex1, rep);
+      splitHistGroup<FT, G>(wh0, wh1, ex, ex1);
     }
     vecWords = ng * G;
   }
@@ -197,8 +212,8 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     if (covered) ckWord(ck, (unsigned long long)((const Word*)in)[off + i], sizeof(Word),
                         (unsigned long long)(off + i) * sizeof(Word), covered);
     splitScalar<FT>(in, off + i, plane0, plane1, rs, e0, e1);
-    splitHistAdd(wh0, e0, rep);
-    if (kPlanes == 2) splitHistAdd(wh1, e1, rep);
+    splitHistAddAt(wh0, e0 << 4);
+    if (kPlanes == 2) splitHistAddAt(wh1, e1 << 4);
   }
   if (covered) *ckAcc ^= ck;
   // zero the section padding after the last word (undefined in the reference)

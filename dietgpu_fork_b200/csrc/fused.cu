@@ -60,8 +60,8 @@ struct FusedParams {
 constexpr uint32_t kFusedThreads = kEncWarps * 32; // 128
 constexpr uint32_t kFusedHistBytes = splitHistWords<kFusedThreads>() * 4;
 constexpr uint32_t kFusedNormBytes = (256 + 16) * 4;
-constexpr uint32_t kFusedSmem =
-    kEncWarps * kEncWarpSmem > kFusedHistBytes + kFusedNormBytes ? kEncWarps * kEncWarpSmem : kFusedHistBytes + kFusedNormBytes;
+constexpr uint32_t kFusedSplitSmem = kSplitHistAlign + kFusedHistBytes + kFusedNormBytes; // bins aligned inside the block
+constexpr uint32_t kFusedSmem = kEncWarps * kEncWarpSmem > kFusedSplitSmem ? kEncWarps * kEncWarpSmem : kFusedSplitSmem;
 
 // Raw ANS (FT == kFtNone): the "split" role only counts bytes; the encode role reads the caller's input.
 // Byte histogram of one 32768-byte tile into the CTA's per-warp replicated bins.
@@ -69,8 +69,7 @@ template <int NT>
 __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t sliceBytes,
                                               uint32_t* sh, uint32_t* ckAcc) {
   const uint32_t tid = threadIdx.x;
-  uint32_t* wh = sh + (tid >> 5) * 256 * kSplitRep;
-  const uint32_t rep = tid & (kSplitRep - 1);
+  const uint32_t wh = smemAddr(sh) + (tid >> 5) * kSplitHistAlign + (tid & (kSplitRep - 1)) * 4u; // see splitHistAddAt
   if (off >= n) return;
   const uint8_t* q = in + off;
   const uint8_t* end = q + min(sliceBytes, n - off);
@@ -79,21 +78,16 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
   const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
   uint32_t ck = 0; // raw ANS: every byte counts
   if (tid < (uint32_t)(a0 - q)) {
-    splitHistAdd(wh, q[tid], rep);
+    splitHistAddAt(wh, (uint32_t)q[tid] << 4);
     ck ^= q[tid];
   }
   if (tid >= 32 && tid - 32 < (uint32_t)(end - a1)) {
-    splitHistAdd(wh, a1[tid - 32], rep);
+    splitHistAddAt(wh, (uint32_t)a1[tid - 32] << 4);
     ck ^= a1[tid - 32];
   }
   const uint4* v = (const uint4*)a0;
   const uint32_t nvec = (uint32_t)(a1 - a0) >> 4;
-  auto addWord = [&](uint32_t x) {
-    splitHistAdd(wh, x & 0xffu, rep);
-    splitHistAdd(wh, (x >> 8) & 0xffu, rep);
-    splitHistAdd(wh, (x >> 16) & 0xffu, rep);
-    splitHistAdd(wh, x >> 24, rep);
-  };
+  auto addWord = [&](uint32_t x) { splitHistAdd4(wh, x); };
   uint32_t i = tid;
   for (; i + 3 * NT < nvec; i += 4 * NT) {
     uint4 x[4];
@@ -157,8 +151,8 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
   __syncthreads();
 
   if (splitRole) {
-    uint32_t* sh = (uint32_t*)smem;
-    uint32_t* normSm = (uint32_t*)(smem + kFusedHistBytes);
+    uint32_t* sh = (uint32_t*)splitHistBase(smem);
+    uint32_t* normSm = sh + kFusedHistBytes / 4;
     for (uint32_t i = tid; i < kFusedHistBytes / 4; i += kFusedThreads) sh[i] = 0;
     // Work is claimed in order, in slices of a tile (p.sliceShift: log2 slices per tile). Counts stay in the CTA's
     // bins while its claims stay inside one element; they go to the element's global bins, followed by the
