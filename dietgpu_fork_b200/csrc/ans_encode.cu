@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "ans_encode.cuh"
+#include "float_split.cuh"
 #include "internal.h"
 #include "knobs.h"
 #include "prof.h"
@@ -42,18 +43,8 @@ int smCount() {
 // 4-way replicated shared-memory bins (lanes l and l+4 share a replica) and flushes to global
 // memory whenever the element changes.
 // ---------------------------------------------------------------------------------------------
-constexpr int kHistRep = 4;
-
-__device__ __forceinline__ void histAdd(uint32_t* wh, uint32_t sym, uint32_t rep) {
-  atomicAdd(&wh[sym * kHistRep + rep], 1u);
-}
-
-__device__ __forceinline__ void histAddWord(uint32_t* wh, uint32_t w, uint32_t rep) {
-  histAdd(wh, w & 0xffu, rep);
-  histAdd(wh, (w >> 8) & 0xffu, rep);
-  histAdd(wh, (w >> 16) & 0xffu, rep);
-  histAdd(wh, w >> 24, rep);
-}
+constexpr int kHistRep = kSplitRep; // same layout and increment as the float split's bins (splitHistAddAt)
+static_assert(kHistRep == 4, "histFlush / splitHistAddAt layout");
 
 // sums the 8 warps x kHistRep replicas of bin `tid`, adds to global, clears
 __device__ __forceinline__ void histFlush(uint32_t* sh, uint32_t* gHist, uint32_t tid) {
@@ -72,18 +63,19 @@ __device__ __forceinline__ void histFlush(uint32_t* sh, uint32_t* gHist, uint32_
   __syncthreads();
 }
 
+constexpr uint32_t kHistBytesSmem = kSplitHistAlign + 8 * 256 * kHistRep * 4; // < 48 KB: no opt-in needed
 __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elems, uint32_t numElems,
                                                    uint32_t totalTiles, uint32_t tilesPerCta,
                                                    uint32_t* __restrict__ hist, uint32_t* __restrict__ normTilesDone,
                                                    uint2* __restrict__ normTable, int normProbBits,
                                                    uint32_t* __restrict__ checksumAcc) {
-  __shared__ uint32_t sh[8 * 256 * kHistRep];
+  extern __shared__ __align__(16) uint8_t smemRaw[]; // kHistBytesSmem: the bins, aligned inside the block
+  uint32_t* const sh = (uint32_t*)splitHistBase(smemRaw);
   __shared__ uint32_t sLast;
   const uint32_t tid = threadIdx.x;
   for (uint32_t i = tid; i < 8 * 256 * kHistRep; i += 256) sh[i] = 0;
   __syncthreads();
-  uint32_t* wh = sh + (tid >> 5) * 256 * kHistRep;
-  const uint32_t rep = tid & (kHistRep - 1);
+  const uint32_t wh = smemAddr(sh) + (tid >> 5) * kSplitHistAlign + (tid & (kHistRep - 1)) * 4u; // see splitHistAddAt
 
   uint32_t t0 = blockIdx.x * tilesPerCta;
   uint32_t t1 = min(t0 + tilesPerCta, totalTiles);
@@ -131,11 +123,11 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
     // head / tail bytes
     uint32_t headN = (uint32_t)(a0 - p), tailN = (uint32_t)(end - a1);
     if (tid < headN) {
-      histAdd(wh, p[tid], rep);
+      splitHistAddAt(wh, (uint32_t)p[tid] << 4);
       ck ^= p[tid];
     }
     if (tid >= 32 && tid - 32 < tailN) {
-      histAdd(wh, a1[tid - 32], rep);
+      splitHistAddAt(wh, (uint32_t)a1[tid - 32] << 4);
       ck ^= a1[tid - 32];
     }
     const uint4* v = (const uint4*)a0;
@@ -143,15 +135,15 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
     uint32_t i = tid;
     for (; i + 768 < nvec; i += 1024) {
       uint4 x0 = v[i], x1 = v[i + 256], x2 = v[i + 512], x3 = v[i + 768];
-      histAddWord(wh, x0.x, rep); histAddWord(wh, x0.y, rep); histAddWord(wh, x0.z, rep); histAddWord(wh, x0.w, rep);
-      histAddWord(wh, x1.x, rep); histAddWord(wh, x1.y, rep); histAddWord(wh, x1.z, rep); histAddWord(wh, x1.w, rep);
-      histAddWord(wh, x2.x, rep); histAddWord(wh, x2.y, rep); histAddWord(wh, x2.z, rep); histAddWord(wh, x2.w, rep);
-      histAddWord(wh, x3.x, rep); histAddWord(wh, x3.y, rep); histAddWord(wh, x3.z, rep); histAddWord(wh, x3.w, rep);
+      splitHistAdd4(wh, x0.x); splitHistAdd4(wh, x0.y); splitHistAdd4(wh, x0.z); splitHistAdd4(wh, x0.w);
+      splitHistAdd4(wh, x1.x); splitHistAdd4(wh, x1.y); splitHistAdd4(wh, x1.z); splitHistAdd4(wh, x1.w);
+      splitHistAdd4(wh, x2.x); splitHistAdd4(wh, x2.y); splitHistAdd4(wh, x2.z); splitHistAdd4(wh, x2.w);
+      splitHistAdd4(wh, x3.x); splitHistAdd4(wh, x3.y); splitHistAdd4(wh, x3.z); splitHistAdd4(wh, x3.w);
       ck ^= x0.x ^ x0.y ^ x0.z ^ x0.w ^ x1.x ^ x1.y ^ x1.z ^ x1.w ^ x2.x ^ x2.y ^ x2.z ^ x2.w ^ x3.x ^ x3.y ^ x3.z ^ x3.w;
     }
     for (; i < nvec; i += 256) {
       uint4 x0 = v[i];
-      histAddWord(wh, x0.x, rep); histAddWord(wh, x0.y, rep); histAddWord(wh, x0.z, rep); histAddWord(wh, x0.w, rep);
+      splitHistAdd4(wh, x0.x); splitHistAdd4(wh, x0.y); splitHistAdd4(wh, x0.z); splitHistAdd4(wh, x0.w);
       ck ^= x0.x ^ x0.y ^ x0.z ^ x0.w;
     }
   }
@@ -166,7 +158,7 @@ int launchHistogram(const Elem* elems, uint32_t numElems, uint32_t totalTiles, u
   ctas = divUp(totalTiles, per);
   {
     ProfScope ps__("k_histBytes", s);
-    k_histBytes<<<ctas, 256, 0, s>>>(elems, numElems, totalTiles, per, hist, normTilesDone, normTable, normProbBits,
+    k_histBytes<<<ctas, 256, kHistBytesSmem, s>>>(elems, numElems, totalTiles, per, hist, normTilesDone, normTable, normProbBits,
                                       checksumAcc);
   }
   DGB_CUDA(cudaGetLastError());
