@@ -252,10 +252,10 @@ int ansDecode(void* temp, size_t tempBytes, int pb, int useChecksum, uint32_t nu
 // Second stream (highest priority) on which the split kernels of the later element groups run
 // while the caller's stream encodes the earlier ones.
 cudaStream_t sideStream() {
-  static thread_local cudaStream_t side[16] = {};
+  static thread_local cudaStream_t side[kMaxDevices] = {};
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 16) return nullptr;
+  if (dev < 0 || dev >= kMaxDevices) return nullptr;
   if (!side[dev]) {
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);

@@ -55,8 +55,10 @@ struct Pipe {
   bool ready = false;
 };
 
-std::mutex g_mutex;
-Pipe g_pipe[16];
+// one pipeline and one lock per device: calls on different GPUs (one thread each) do not serialise each other; two
+// calls on the same GPU share its lanes and take turns
+std::mutex g_mutex[kMaxDevices];
+Pipe g_pipe[kMaxDevices];
 
 int lanePrepare(Lane& l, size_t devBytes, size_t pinnedBytes) {
   if (!l.s) {
@@ -181,8 +183,8 @@ struct EntryGuard { // the caller's stream orders the call: lanes start after it
   std::unique_lock<std::mutex> lock;
   int begin(cudaStream_t user) {
     DGB_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 16) return kErrInvalidArg;
-    lock = std::unique_lock<std::mutex>(g_mutex);
+    if (dev < 0 || dev >= kMaxDevices) return kErrInvalidArg;
+    lock = std::unique_lock<std::mutex>(g_mutex[dev]);
     pipe = &g_pipe[dev];
     for (int k = 0; k < kPipeLanes; ++k) {
       int rc = lanePrepare(pipe->lane[k], 0, 0);
@@ -432,10 +434,10 @@ int dgb_ans_decode_host(int pb, int cs, uint32_t num, const void* const* in, con
 }
 
 void dgb_host_release(void) {
-  std::lock_guard<std::mutex> lock(g_mutex);
   int cur = 0;
   cudaGetDevice(&cur);
-  for (int d = 0; d < 16; ++d) {
+  for (int d = 0; d < kMaxDevices; ++d) {
+    std::lock_guard<std::mutex> lock(g_mutex[d]);
     Pipe& p = g_pipe[d];
     bool any = false;
     for (int k = 0; k < kPipeLanes; ++k) any = any || p.lane[k].s;
