@@ -529,7 +529,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
 // sizes coalesceTileWarp sums up are final and the tile's own slots are complete. Whole groups before the tile's
 // group are checked through the group counters, the tiles of its own group one per lane. Runs are handed out in
 // order, so in steady state the first look succeeds.
-// `wait` false: one look, returns whether the tile is ready (used between runs, where a warp must not block).
+// `wait` false: one look, returns whether the tile is ready (for callers that must not block).
 static __device__ __noinline__ bool waitTilesEncoded(const EncParams& p, uint32_t e, uint32_t tk, uint32_t lane,
                                                      bool wait) {
   const Elem el = p.a.elems[e];

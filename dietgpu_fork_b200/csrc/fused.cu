@@ -53,7 +53,6 @@ struct FusedParams {
   uint32_t* splitCounterB; // zeroed: claims beyond the fine prefix
   uint32_t tailSlices;     // the last tailSlices slices are claimed tailClaim at a time (short stragglers)
   uint32_t tailClaim;
-  uint32_t compactBetweenRuns; // few huge elements: warps compact finished tiles between their runs
   unsigned long long* trace; // nullable (DGB_FUSED_TRACE): per CTA {start, split end, first run end, end, smid/role, encode end}
 };
 
@@ -105,29 +104,6 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
     ck ^= x.x ^ x.y ^ x.z ^ x.w;
   }
   if (ckAcc) *ckAcc ^= ck;
-}
-
-// Between runs (batches of few huge elements only, where compaction would otherwise be a serial tail after the
-// last run): if the next compaction tile is already completely encoded, with everything before it in its element,
-// try to take exactly that ticket and compact it now, while its slots are hot in L2. A warp never blocks here (it
-// may hold the only claim on a run others wait for); the staging area is the warp's stage + ring, its encode
-// table stays intact. Not inlined: it must not take registers from the row loop.
-template <int PB>
-static __device__ __noinline__ void tryCompactOne(const FusedParams& p, uint32_t lane, uint8_t* stage) {
-  uint32_t tk = 0;
-  if (lane == 0) tk = ldRelaxed(p.coalClaim);
-  tk = __shfl_sync(0xffffffffu, tk, 0);
-  if (tk >= p.totalTiles) return;
-  uint32_t guess = 0;
-  const uint32_t ce = findElement(&p.sp.elems[0].tileBase, sizeof(Elem) / 4, p.sp.numElems, tk, guess);
-  if (!waitTilesEncoded(p.ep, ce, tk, lane, false)) return;
-  uint32_t got = 0;
-  if (lane == 0) got = atomicCAS(p.coalClaim, tk, tk + 1u) == tk ? 1u : 0u;
-  got = __shfl_sync(0xffffffffu, got, 0);
-  if (!got) return;
-  __syncwarp();
-  coalesceTileWarp(p.ep, PB, ce, tk, lane, stage, kEncStageBytes + kEncRingBytes);
-  __syncwarp(); // stage and ring are free for the next run
 }
 
 template <int FT, int PB>
@@ -265,7 +241,6 @@ __global__ void __launch_bounds__(kFusedThreads, kEncCtasPerSm) k_compressFused(
     if (w.lane == 0) nextRun = atomicAdd(p.ep.runCounter, 1u);
     encodeRun<PB, true>(p.ep, w, run);
     if (p.trace && tid == 0 && t2 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2)); // end of first run
-    if (p.compactBetweenRuns) tryCompactOne<PB>(p, w.lane, w.stage);
     run = __shfl_sync(0xffffffffu, nextRun, 0);
   }
   if (p.trace && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tEnc));
@@ -324,15 +299,11 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
   p.sliceShift = 3;
   p.splitClaim = 16;
   p.fineSlices = 0;
-  p.compactBetweenRuns = 0;
   {
     const uint64_t splitCtas = (uint64_t)splitPerSm * (uint64_t)smCount();
     if (DGB_KNOB("DGB_SPLIT_FINE_TILES", 0) > 0) p.fineSlices = (uint32_t)DGB_KNOB("DGB_SPLIT_FINE_TILES", 0) << p.sliceShift; // experiment knob
     if ((uint64_t)p.totalTiles >= splitCtas * (uint64_t)p.sp.numElems) {
       p.fineSlices = 0xfffffff0u; // everything
-      // and compaction is interleaved with the runs (fp32 1 x 1 GiB: 0.682 -> 0.669 ms; for batches of many
-      // elements, whose compaction overlaps the encoding of later elements anyway, it costs 3 %)
-      p.compactBetweenRuns = 1;
       p.splitClaim = 16;
       // nothing can be encoded before the first table exists and there are few tables to wait for: all CTAs
       // but one per SM split (fp32 1 x 1 GiB on B200: 0.73 ms with 3 split CTAs per SM and whole tiles,
@@ -346,8 +317,6 @@ static int launchFusedT(FusedParams& p, cudaStream_t s) {
       p.tailSlices = rounds * (uint32_t)splitCtas * p.splitClaim;
       p.tailClaim = tail;
     }
-    if (DGB_KNOB("DGB_COMPACT_BETWEEN_RUNS", -1) >= 0) p.compactBetweenRuns = DGB_KNOB("DGB_COMPACT_BETWEEN_RUNS", -1) != 0; // experiment knob
-    if (!p.coalClaim) p.compactBetweenRuns = 0;
     if (p.fineSlices > (p.totalTiles << p.sliceShift)) p.fineSlices = p.totalTiles << p.sliceShift;
     p.fineSlices = p.fineSlices / p.splitClaim * p.splitClaim;
   }
