@@ -535,7 +535,27 @@ static __device__ __noinline__ bool waitTilesEncoded(const EncParams& p, uint32_
   const Elem el = p.a.elems[e];
   const uint32_t t = tk - el.tileBase;
   const uint32_t nb = divUp(el.n, kBlockSyms);
-  if (t * kTileBlocks >= nb) return true; // no blocks in this tile (empty element or padding tile)
+  if (t * kTileBlocks >= nb) {
+    // No blocks in this tile (empty element or padding tile), so no finished block vouches for the element's split:
+    // wait for its ready flag instead. The split role writes the float header (zeroing firstCompSegmentBytes) and
+    // the compaction that follows this call fills that field in - an idle warp that took an empty element's tile at
+    // the start of the kernel used to get there first, and the header write then wiped the size (seen as an
+    // occasional wrong byte 16 of an EMPTY element's archive in batches small enough to leave warps without runs).
+    if (p.ready) {
+      uint32_t ok = 1;
+      if (lane == 0) {
+        uint32_t ns = 100;
+        while ((ok = ldRelaxed(p.ready + e)) == 0 && wait) {
+          __nanosleep(ns);
+          if (ns < 1600) ns *= 2;
+        }
+      }
+      ok = __shfl_sync(0xffffffffu, ok, 0);
+      if (!ok) return false;
+      asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    }
+    return true;
+  }
   constexpr uint32_t kGroupTiles = kGroupBlocks / kTileBlocks;
   const uint32_t grp = t / kGroupTiles;
   const uint32_t* groupSum = p.groupWords + el.groupBase;

@@ -55,3 +55,35 @@ def test_repeated_compress_is_deterministic(ft, batch, words, iters):
         bad += sum((o.view(torch.int16) != t.view(torch.int16)).sum() for o, t in zip(outs, ins)) if it % 10 == 0 else 0
     torch.cuda.synchronize()
     assert int(bad.item()) == 0 and bool(ok.all())
+
+
+def test_fused_small_ragged_batch_with_empty_elements_is_deterministic():
+    """Regression (round 2): in a batch small enough to leave most warps of the fused kernel without an encode run,
+    an idle warp took the compaction ticket of an EMPTY element at the start of the kernel, filled in the float
+    header's firstCompSegmentBytes, and the split role's header write - which nothing ordered before it, because no
+    encoded block vouches for an empty element - zeroed it again: about one run in seven. 300 runs of that shape under
+    the fused schedule against the separate-launch schedule's archives, every byte."""
+    import numpy as np
+    import gpu_harness as H
+    counts = [9 * 1024 * 1024, 1, 0, 4097, 3 * 1024 * 1024 + 5, 33, 0, 0, 70000]
+    g = torch.Generator(device="cuda").manual_seed(99)
+    ins = [(torch.randn(n, device="cuda", generator=g) * 0.02).to(torch.float16).view(torch.int16) for n in counts]
+    try:
+        _capi.lib.dgb_set_fused_min_tiles(1 << 40)
+        want, want_sizes = H.ours_float_compress(1, ins, counts, 10)
+        _capi.lib.dgb_set_fused_min_tiles(0)
+        mx = want.shape[1]
+        comp = torch.empty_like(want)
+        rows = [comp[i] for i in range(len(counts))]
+        sizes = torch.zeros(len(counts), dtype=torch.int32, device="cuda")
+        ws = torch.from_numpy(np.asarray(want_sizes)).to("cuda", torch.int32)
+        valid = torch.arange(mx, device="cuda").unsqueeze(0) < ws.to(torch.int64).unsqueeze(1)
+        bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+        for _ in range(300):
+            comp.fill_(0xA5)
+            codec.float_compress(1, ins, rows, sizes, 10, False, in_sizes=counts)
+            bad += ((comp != want) & valid).sum() + (sizes != ws).sum()
+        torch.cuda.synchronize()
+    finally:
+        _capi.lib.dgb_set_fused_min_tiles(-1)
+    assert int(bad.item()) == 0, f"{int(bad.item())} bytes / sizes differed from the separate-launch archives over 300 runs"
