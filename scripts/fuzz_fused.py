@@ -1,7 +1,8 @@
 """Randomised search for timing-dependent differences in the fused compress kernel: random small / ragged batch
 shapes (including empty and one-word elements, which leave most warps of the persistent kernel without an encode
 run), ANS bytes and f16 / bf16 / f32 words, checksum on and off; each shape compressed `reps` times under the fused
-schedule and compared byte for byte with the separate-launch schedule's archives, then decoded once.
+schedule and compared byte for byte with the separate-launch schedule's archives, then decoded reps / 3 times; bf16 /
+f32 shapes without checksum also go through the sparse codec (90 % zeros), whose compaction has its own look-back.
 `python scripts/fuzz_fused.py [shapes] [reps] [seed]` on the GPU. Prints every difference; exit code 1 if any."""
 import sys
 
@@ -64,15 +65,44 @@ def run(shapes, reps, seed):
         finally:
             _capi.lib.dgb_set_fused_min_tiles(-1)
         rows = [mf[i] for i in range(k)]
-        if ft == 0:
-            outs, ok, dsz = H.ours_ans_decode(rows, counts, 10, checksum=cs)
-        else:
-            outs, ok, dsz = H.ours_float_decompress(ft, rows, counts, 10, checksum=cs)
         wb = {0: 1, 1: 2, 2: 2, 3: 4}[ft]
-        for i, t in enumerate(ins):
-            if not (ok[i] and torch.equal(outs[i][:counts[i] * wb], t.view(torch.uint8).reshape(-1))):
-                bad += 1
-                print(f"shape {s} ft {ft} cs {cs} {counts} element {i}: round trip differs (ok {ok[i]})", flush=True)
+        for r in range(max(1, reps // 3)):  # the decoder claims its tiles dynamically too
+            if ft == 0:
+                outs, ok, dsz = H.ours_ans_decode(rows, counts, 10, checksum=cs)
+            else:
+                outs, ok, dsz = H.ours_float_decompress(ft, rows, counts, 10, checksum=cs)
+            for i, t in enumerate(ins):
+                if not (ok[i] and torch.equal(outs[i][:counts[i] * wb], t.view(torch.uint8).reshape(-1))):
+                    bad += 1
+                    print(f"shape {s} ft {ft} cs {cs} {counts} decode {r} element {i}: round trip differs (ok {ok[i]})",
+                          flush=True)
+        if ft in (2, 3) and not cs and min(counts) >= 2:
+            bad += sparse_round(s, ft, counts, reps)
+    return bad
+
+
+def sparse_round(s, ft, counts, reps):
+    """The sparse codec's compaction uses a decoupled look-back between CTAs: same shape with 90 % zeros, `reps`
+    compressions compared with the first, one decode."""
+    bad = 0
+    g = torch.Generator(device="cuda").manual_seed(5000 + s)
+    ins = []
+    for i, n in enumerate(counts):
+        t = make(ft, n, 9000 * s + i).clone()
+        t[torch.rand(n, device="cuda", generator=g) < 0.9] = 0
+        ins.append(t)
+    first, fs = H.ours_float_compress(ft, ins, counts, 10, sparse=True, fill=0xA5)
+    for r in range(reps):
+        m, sz = H.ours_float_compress(ft, ins, counts, 10, sparse=True, fill=0xA5)
+        if list(sz) != list(fs) or any(not torch.equal(m[i, :sz[i]], first[i, :fs[i]]) for i in range(len(counts))):
+            bad += 1
+            print(f"shape {s} sparse ft {ft} {counts} rep {r}: archives differ from the first run", flush=True)
+    outs, ok, dsz = H.ours_float_decompress(ft, [first[i] for i in range(len(counts))], counts, 10, sparse=True)
+    wb = 2 if ft == 2 else 4
+    for i, t in enumerate(ins):
+        if not torch.equal(outs[i][:counts[i] * wb], t.view(torch.uint8).reshape(-1)):
+            bad += 1
+            print(f"shape {s} sparse ft {ft} {counts} element {i}: round trip differs", flush=True)
     return bad
 
 
