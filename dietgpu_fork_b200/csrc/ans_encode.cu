@@ -40,11 +40,11 @@ int smCount() {
 
 // ---------------------------------------------------------------------------------------------
 // Byte histogram. Each CTA owns a contiguous range of tiles, accumulates into per-warp,
-// 4-way replicated shared-memory bins (lanes l and l+4 share a replica) and flushes to global
+// shared-memory bins (kSplitRep replicas, float_split.cuh) and flushes to global
 // memory whenever the element changes.
 // ---------------------------------------------------------------------------------------------
 constexpr int kHistRep = kSplitRep; // same layout and increment as the float split's bins (splitHistAddAt)
-static_assert(kHistRep == 4, "histFlush / splitHistAddAt layout");
+
 
 // sums the 8 warps x kHistRep replicas of bin `tid`, adds to global, clears
 __device__ __forceinline__ void histFlush(uint32_t* sh, uint32_t* gHist, uint32_t tid) {
@@ -123,11 +123,11 @@ __global__ void __launch_bounds__(256) k_histBytes(const Elem* __restrict__ elem
     // head / tail bytes
     uint32_t headN = (uint32_t)(a0 - p), tailN = (uint32_t)(end - a1);
     if (tid < headN) {
-      splitHistAddAt(wh, (uint32_t)p[tid] << 4);
+      splitHistAddAt(wh, (uint32_t)p[tid] << kSplitSymShift);
       ck ^= p[tid];
     }
     if (tid >= 32 && tid - 32 < tailN) {
-      splitHistAddAt(wh, (uint32_t)a1[tid - 32] << 4);
+      splitHistAddAt(wh, (uint32_t)a1[tid - 32] << kSplitSymShift);
       ck ^= a1[tid - 32];
     }
     const uint4* v = (const uint4*)a0;

@@ -5,7 +5,7 @@
 // bits go straight into the final archive, the exponent bytes into a temp plane that the ANS encoder reads
 // next, and the float header is written by the element's first tile. Differences in how: work is cut into
 // 32768-word tiles, each thread handles one 16-byte input vector per step with warp-contiguous loads and
-// stores, histograms live in per-warp 4-way replicated shared-memory bins, and all padding the reference
+// stores, histograms live in per-warp shared-memory bins, and all padding the reference
 // leaves undefined is written as 0.
 #pragma once
 #include "float_math.cuh"
@@ -13,7 +13,16 @@
 
 namespace dgb {
 
-constexpr int kSplitRep = 4;
+// Replicas of a warp's bins (1, 2 or 4; lane l counts into replica l % kSplitRep). One: `ATOMS.POPC.INC` merges the
+// lanes of an instruction that hit the same counter, and what an increment costs follows the number of DISTINCT
+// counters it touches - replicas only multiply those. B200, replicas 4 / 2 / 1: fp16 128 x 4 MiB 0.480 / 0.470 /
+// 0.461 ms, fp64 16 x 8 MiB 0.146 / 0.141 / 0.141, ANS 16 x 1 MiB 59.1 / 58.3 / 57.9 us, bf16 and fp32 equal.
+#ifndef DGB_SPLIT_REP
+#define DGB_SPLIT_REP 1
+#endif
+constexpr int kSplitRep = DGB_SPLIT_REP;
+constexpr uint32_t kSplitSymShift = kSplitRep == 4 ? 4 : kSplitRep == 2 ? 3 : 2; // a symbol's place in a counter's address
+static_assert(kSplitRep == 1 || kSplitRep == 2 || kSplitRep == 4, "");
 constexpr uint32_t kSplitPrefetchVecs = 2048; // 32 KB ahead of the loads
 template <int NT> __host__ __device__ constexpr uint32_t splitHistWords() { return (NT / 32) * 256 * kSplitRep; } // per plane
 
@@ -48,27 +57,28 @@ struct SplitParams {
   int normProbBits;
 };
 
-// The CTA's bins start at a 4096-byte aligned SHARED address (splitHistBase): a warp's 256 x kSplitRep counters are
-// 4 KB, so a counter's address is  warp base | symbol << 4 | replica << 2  and an increment costs a shift, one LOP3
-// and the ATOMS (an index the compiler has to add to a base costs one instruction more per symbol).
-constexpr uint32_t kSplitHistAlign = 256 * kSplitRep * 4; // 4096
-static_assert(kSplitHistAlign == 4096, "one warp's bins = address bits 2..11");
+// The CTA's bins start at a SHARED address aligned to one warp's bins (splitHistBase): a warp's 256 x kSplitRep
+// counters are 1 KB (x kSplitRep), so a counter's address is  warp base | symbol << kSplitSymShift | replica << 2
+// and an increment costs a shift, one LOP3 and the ATOMS (an index the compiler has to add to a base costs one
+// instruction more per symbol).
+constexpr uint32_t kSplitHistAlign = 256 * kSplitRep * 4;
 // first kSplitHistAlign-aligned byte of a dynamic shared-memory block (callers allocate kSplitHistAlign more)
 __device__ __forceinline__ uint8_t* splitHistBase(uint8_t* smem) {
   const uint32_t a = smemAddr(smem);
   return smem + ((kSplitHistAlign - (a & (kSplitHistAlign - 1u))) & (kSplitHistAlign - 1u));
 }
-// whRep: shared address of the warp's bins | replica * 4; symShl4: the symbol at bits 4..11, anything elsewhere
-__device__ __forceinline__ void splitHistAddAt(uint32_t whRep, uint32_t symShl4) {
-  const uint32_t addr = (symShl4 & 0xff0u) | whRep;
+// whRep: shared address of the warp's bins | replica * 4; symShl: the symbol shifted left by kSplitSymShift, anything
+// elsewhere
+__device__ __forceinline__ void splitHistAddAt(uint32_t whRep, uint32_t symShl) {
+  const uint32_t addr = (symShl & (0xffu << kSplitSymShift)) | whRep;
   asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
 }
 // the four bytes of x
 __device__ __forceinline__ void splitHistAdd4(uint32_t whRep, uint32_t x) {
-  splitHistAddAt(whRep, x << 4);
-  splitHistAddAt(whRep, x >> 4);
-  splitHistAddAt(whRep, x >> 12);
-  splitHistAddAt(whRep, x >> 20);
+  splitHistAddAt(whRep, x << kSplitSymShift);
+  splitHistAddAt(whRep, x >> (8 - kSplitSymShift));
+  splitHistAddAt(whRep, x >> (16 - kSplitSymShift));
+  splitHistAddAt(whRep, x >> (24 - kSplitSymShift));
 }
 
 // sums the warps x replicas of the bins this thread owns, adds to global, clears. Callers bracket it with
@@ -100,10 +110,10 @@ __device__ __forceinline__ void splitHistGroup(uint32_t wh0, uint32_t wh1, const
   } else if constexpr (G == 4) {
     splitHistAdd4(wh0, ex[0]);
   } else {
-    splitHistAddAt(wh0, ex[0] << 4);
-    splitHistAddAt(wh0, ex[0] >> 4);
-    splitHistAddAt(wh1, ex1[0] << 4);
-    splitHistAddAt(wh1, ex1[0] >> 4);
+    splitHistAddAt(wh0, ex[0] << kSplitSymShift);
+    splitHistAddAt(wh0, ex[0] >> (8 - kSplitSymShift));
+    splitHistAddAt(wh1, ex1[0] << kSplitSymShift);
+    splitHistAddAt(wh1, ex1[0] >> (8 - kSplitSymShift));
   }
 }
 
@@ -212,8 +222,8 @@ __device__ __forceinline__ void splitTile(const SplitParams& p, uint32_t e, cons
     if (covered) ckWord(ck, (unsigned long long)((const Word*)in)[off + i], sizeof(Word),
                         (unsigned long long)(off + i) * sizeof(Word), covered);
     splitScalar<FT>(in, off + i, plane0, plane1, rs, e0, e1);
-    splitHistAddAt(wh0, e0 << 4);
-    if (kPlanes == 2) splitHistAddAt(wh1, e1 << 4);
+    splitHistAddAt(wh0, e0 << kSplitSymShift);
+    if (kPlanes == 2) splitHistAddAt(wh1, e1 << kSplitSymShift);
   }
   if (covered) *ckAcc ^= ck;
   // zero the section padding after the last word (undefined in the reference)

@@ -66,7 +66,7 @@ constexpr uint32_t kFusedSplitSmem = kSplitHistAlign + kFusedHistBytes + kFusedN
 constexpr uint32_t kFusedSmem = kEncWarps * kEncWarpSmem > kFusedSplitSmem ? kEncWarps * kEncWarpSmem : kFusedSplitSmem;
 
 // Raw ANS (FT == kFtNone): the "split" role only counts bytes; the encode role reads the caller's input.
-// Byte histogram of one 32768-byte tile into the CTA's per-warp replicated bins.
+// Byte histogram of one 32768-byte tile into the CTA's per-warp bins.
 template <int NT>
 __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uint32_t off, uint32_t sliceBytes,
                                               uint32_t* sh, uint32_t* ckAcc) {
@@ -80,11 +80,11 @@ __device__ __forceinline__ void histTileBytes(const uint8_t* in, uint32_t n, uin
   const uint8_t* a1 = a0 + ((size_t)(end - a0) & ~(size_t)15);
   uint32_t ck = 0; // raw ANS: every byte counts
   if (tid < (uint32_t)(a0 - q)) {
-    splitHistAddAt(wh, (uint32_t)q[tid] << 4);
+    splitHistAddAt(wh, (uint32_t)q[tid] << kSplitSymShift);
     ck ^= q[tid];
   }
   if (tid >= 32 && tid - 32 < (uint32_t)(end - a1)) {
-    splitHistAddAt(wh, (uint32_t)a1[tid - 32] << 4);
+    splitHistAddAt(wh, (uint32_t)a1[tid - 32] << kSplitSymShift);
     ck ^= a1[tid - 32];
   }
   const uint4* v = (const uint4*)a0;
