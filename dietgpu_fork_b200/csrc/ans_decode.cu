@@ -640,7 +640,6 @@ __global__ void __launch_bounds__(kDecWarps * 32, FT == kFtF64 ? 4 : 6) k_decode
 
 template <int PB, int FT>
 static int launchDecodeKernel(DecParams& p, cudaStream_t s) {
-  constexpr int kPlanes = FT == kFtF64 ? 2 : 1;
   constexpr uint32_t smemBytes = decCtaSmem<PB, FT>();
   {
     static DeviceOnce once;
