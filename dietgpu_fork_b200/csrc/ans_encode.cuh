@@ -292,6 +292,9 @@ __device__ __forceinline__ uint32_t ldRelaxed(const uint32_t* p) {
 __device__ __forceinline__ void redRelease(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void redRelaxed(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void stRelease(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -439,8 +442,10 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
           DGB_TRACE_MAX(w.curElem, 2);
           // sizes and, in the high bits, the number of finished blocks (release: slot and size first); the
           // in-kernel compaction of a tile starts as soon as these counts say its predecessors are encoded
-          redRelease(&w.groupSum[blk / kGroupBlocks], paddedWords + kGroupCountOne);
-          redRelease(p.tileWords + w.tileBase + blk / kTileBlocks, paddedWords + kTileCountOne);
+          // (one release fence for both counters: two red.release cost two waits for the block's stores)
+          asm volatile("fence.acq_rel.gpu;" ::: "memory");
+          redRelaxed(&w.groupSum[blk / kGroupBlocks], paddedWords + kGroupCountOne);
+          redRelaxed(p.tileWords + w.tileBase + blk / kTileBlocks, paddedWords + kTileCountOne);
         } else {
           atomicAdd(&w.groupSum[blk / kGroupBlocks], paddedWords);
         }
