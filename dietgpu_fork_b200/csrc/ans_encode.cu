@@ -235,7 +235,12 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 // Stand-alone block encoder (see encodeRun in ans_encode.cuh). A warp's first run is static, further
 // runs are handed out in order by an atomic counter (fetched one run ahead), so the resident warps
 // always stream one contiguous window of the input and finish together.
-template <int PB>
+// COMPACT: the warps also do k_coalesce's job once they are out of runs, as in the fused kernel (tickets for 8-block
+// tiles in order, each waiting until the tile and its predecessors in the element are encoded): one launch less and
+// the first tiles are compacted while the last blocks are still being encoded. The grid is co-resident (at most
+// kEncCtasPerSm CTAs per SM, which the launch bounds and the shared-memory size guarantee), so every run is owned by
+// a running warp and the waits end.
+template <int PB, bool COMPACT>
 __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t wi = threadIdx.x >> 5;
@@ -246,8 +251,23 @@ __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const 
   while (run < numRuns) {
     uint32_t nextRun = 0;
     if (w.lane == 0) nextRun = p.totalWarps + atomicAdd(p.runCounter, 1u);
-    encodeRun<PB, false>(p, w, run);
+    encodeRun<PB, COMPACT>(p, w, run);
     run = __shfl_sync(0xffffffffu, nextRun, 0);
+  }
+  if constexpr (COMPACT) {
+    const uint32_t tiles = p.tileEnd - p.tileBegin;
+    uint32_t guess = 0;
+    for (;;) {
+      uint32_t tk = 0;
+      if (w.lane == 0) tk = atomicAdd(p.coalClaim, 1u);
+      tk = __shfl_sync(0xffffffffu, tk, 0);
+      if (tk >= tiles) break;
+      tk += p.tileBegin;
+      const uint32_t ce = findElement(&p.a.elems[0].tileBase, sizeof(Elem) / 4, p.a.numElems, tk, guess);
+      guess = ce;
+      (void)waitTilesEncoded(p, ce, tk, w.lane, true);
+      coalesceTileWarp(p, PB, ce, tk, w.lane, w.tabSmem, kEncWarpSmem);
+    }
   }
 }
 
@@ -361,6 +381,7 @@ void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, c
   p.runCounter = es.runCounters + r.e0;
   p.ready = nullptr;
   p.tileWords = nullptr;
+  p.coalClaim = nullptr;
   p.tileBegin = r.tile0;
   p.tileEnd = r.tile1;
   p.totalWarps = 0;
@@ -386,9 +407,22 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * perSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
+  // Compaction inside the encoder launch when this launch covers the whole work list (the grouped schedule's
+  // ranges share one ticket counter and keep k_coalesce). Needs the per-tile sums the fused kernel uses.
+  // Only from 1024 tiles (more blocks than resident warps): a tile costs ONE warp about 10 us of dependent loads here against a CTA of eight in
+  // k_coalesce, which pays only when there are later waves of blocks to hide it behind (B200, separate / in-kernel:
+  // bf16 1 x 64 MiB = 1024 tiles 0.0999 / 0.0949 ms, but 4 x 8 MiB = 512 tiles 0.0534 / 0.0591, ANS 16 x 1 MiB 57.0 / 60.4 us, fp64
+  // 16 x 8 MiB 0.1408 / 0.1458, sparse 0.2106 / 0.2155).
+  const bool whole = r.e0 == 0 && r.e1 == a.numElems && r.tile0 == 0;
+  bool compact = whole && es.fusedCtrl && r.tile1 - r.tile0 >= 1024;
+  if (DGB_KNOB("DGB_ENC_COMPACT", -1) >= 0) compact = whole && es.fusedCtrl && DGB_KNOB("DGB_ENC_COMPACT", -1) != 0; // experiment knob
+  if (compact) {
+    p.tileWords = es.fusedCtrl + kFusedCtrlFixed + 3 * (size_t)a.numElems;
+    p.coalClaim = es.fusedCtrl + kFusedCtrlCoal;
+  }
   auto launch = [&](auto kern) -> int {
-    static DeviceOnce onceByPb[3]; // the three instantiations share one function-pointer type
-    DeviceOnce& once = onceByPb[a.probBits - 9];
+    static DeviceOnce onceByPb[6]; // the instantiations share one function-pointer type
+    DeviceOnce& once = onceByPb[(a.probBits - 9) * 2 + (compact ? 1 : 0)];
     const int dev = currentDevice();
     if (once.first(dev)) {
       DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
@@ -403,12 +437,12 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   };
   int rc;
   switch (a.probBits) {
-    case 9: rc = launch(k_encode<9>); break;
-    case 10: rc = launch(k_encode<10>); break;
-    default: rc = launch(k_encode<11>); break;
+    case 9: rc = compact ? launch(k_encode<9, true>) : launch(k_encode<9, false>); break;
+    case 10: rc = compact ? launch(k_encode<10, true>) : launch(k_encode<10, false>); break;
+    default: rc = compact ? launch(k_encode<11, true>) : launch(k_encode<11, false>); break;
   }
   if (rc) return rc;
-  return launchCoalesce(a, es, r, s);
+  return compact ? kOk : launchCoalesce(a, es, r, s);
 }
 
 int launchCoalesce(const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r, cudaStream_t s) {

@@ -161,6 +161,9 @@ struct EncParams {
   uint32_t runShift;           // log2(runs per tile): runs are 8 >> runShift consecutive blocks
   // fused kernel only: per-element flag, non-zero once the element's exponent plane and table are complete
   const uint32_t* ready;
+  // stand-alone encoder with in-kernel compaction (k_encode<PB, true>): zeroed ticket counter for the launch's tiles;
+  // tileWords is then set as in the fused kernel, ready stays null (the tables exist before the launch)
+  uint32_t* coalClaim;
 };
 
 void fillEncParams(EncParams& p, const EncodeArgs& a, const EncodeScratch& es, const WorkRange& r);
@@ -372,7 +375,7 @@ __device__ __forceinline__ void encodeRun(const EncParams& p, EncWarp& w, uint32
     w.blockBase = el.blockBase;
     w.groupSum = p.groupWords + el.groupBase;
     w.elemSrc = a.planeBase ? a.planeBase + el.planeOff : (const uint8_t*)el.in;
-    if (FUSED) {
+    if (FUSED && p.ready) {
       if (lane == 0) { // relaxed polling with growing back-off (an acquire load per poll would flush L1 each time)
 #ifdef DGB_TRACE_ELEMS
         const unsigned long long tw0 = traceNow();
@@ -539,7 +542,7 @@ static __device__ __noinline__ bool waitTilesEncoded(const EncParams& p, uint32_
                                                      bool wait) {
   const Elem el = p.a.elems[e];
   const uint32_t t = tk - el.tileBase;
-  const uint32_t nb = divUp(el.n, kBlockSyms);
+  const uint32_t nb = divUp(p.a.nDev ? p.a.nDev[e] : el.n, kBlockSyms); // device-side sizes: blocks beyond them never come
   if (t * kTileBlocks >= nb) {
     // No blocks in this tile (empty element or padding tile), so no finished block vouches for the element's split:
     // wait for its ready flag instead. The split role writes the float header (zeroing firstCompSegmentBytes) and
