@@ -404,6 +404,7 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   const uint32_t runs = (r.tile1 - r.tile0) << p.runShift;
   uint32_t perSm = kEncCtasPerSm;
   if (DGB_KNOB("DGB_ENC_CTAS", 0) > 0) perSm = (uint32_t)DGB_KNOB("DGB_ENC_CTAS", 0); // experiment knob
+  if (perSm > kEncCtasPerSm) perSm = kEncCtasPerSm; // never more CTAs than are resident at once: with in-kernel compaction warps wait for runs other CTAs hold
   const uint32_t grid = min(divUp(runs, kEncWarps), (uint32_t)smCount() * perSm);
   p.totalWarps = grid * kEncWarps;
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
