@@ -237,9 +237,9 @@ __global__ void __launch_bounds__(256) k_normalize(const Elem* __restrict__ elem
 // always stream one contiguous window of the input and finish together.
 // COMPACT: the warps also do k_coalesce's job once they are out of runs, as in the fused kernel (tickets for 8-block
 // tiles in order, each waiting until the tile and its predecessors in the element are encoded): one launch less and
-// the first tiles are compacted while the last blocks are still being encoded. The grid is co-resident (at most
-// kEncCtasPerSm CTAs per SM, which the launch bounds and the shared-memory size guarantee), so every run is owned by
-// a running warp and the waits end.
+// the first tiles are compacted while the last blocks are still being encoded. Every run is owned by a running warp
+// (all of them are claimed from the counter in this mode) and encoding warps never wait, so the waits end whether or
+// not the whole grid is resident.
 template <int PB, bool COMPACT>
 __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const EncParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -248,6 +248,13 @@ __global__ void __launch_bounds__(kEncWarps * 32, kEncCtasPerSm) k_encode(const 
   w.init(smem + wi * kEncWarpSmem);
   const uint32_t numRuns = (p.tileEnd - p.tileBegin) << p.runShift;
   uint32_t run = blockIdx.x * kEncWarps + wi;
+  if constexpr (COMPACT) {
+    // every run is claimed, the first one too (p.totalWarps is 0): a run must belong to a RUNNING warp, because
+    // warps wait for runs below; a statically assigned run of a CTA that is not resident yet (another stream's
+    // kernel may hold its place) could be waited for by every resident warp
+    if (w.lane == 0) run = atomicAdd(p.runCounter, 1u);
+    run = __shfl_sync(0xffffffffu, run, 0);
+  }
   while (run < numRuns) {
     uint32_t nextRun = 0;
     if (w.lane == 0) nextRun = p.totalWarps + atomicAdd(p.runCounter, 1u);
@@ -410,16 +417,18 @@ int launchAnsEncode(const EncodeArgs& a, const EncodeScratch& es, const WorkRang
   const uint32_t smemBytes = kEncWarps * kEncWarpSmem;
   // Compaction inside the encoder launch when this launch covers the whole work list (the grouped schedule's
   // ranges share one ticket counter and keep k_coalesce). Needs the per-tile sums the fused kernel uses.
-  // Only from 1024 tiles (more blocks than resident warps): a tile costs ONE warp about 10 us of dependent loads here against a CTA of eight in
-  // k_coalesce, which pays only when there are later waves of blocks to hide it behind (B200, separate / in-kernel:
-  // bf16 1 x 64 MiB = 1024 tiles 0.0999 / 0.0949 ms, but 4 x 8 MiB = 512 tiles 0.0534 / 0.0591, ANS 16 x 1 MiB 57.0 / 60.4 us, fp64
-  // 16 x 8 MiB 0.1408 / 0.1458, sparse 0.2106 / 0.2155).
+  // Off by default (DGB_ENC_COMPACT=1 turns it on): a tile costs ONE warp about 10 us of dependent loads here against
+  // a CTA of eight in k_coalesce, which pays only when later waves of blocks hide it (B200, separate / in-kernel:
+  // bf16 1 x 64 MiB = 1024 tiles 0.0999 / 0.0949 ms, but 4 x 8 MiB = 512 tiles 0.0534 / 0.0591, ANS 16 x 1 MiB
+  // 57.0 / 60.4 us, fp64 16 x 8 MiB 0.1408 / 0.1458, sparse 0.2106 / 0.2155) - and that gain needed each warp's
+  // first run to be assigned statically, which is not safe when the grid is only partly resident (a second stream's
+  // kernel on the same GPU): with every run claimed from the counter, as it has to be, 1 x 64 MiB takes 0.1048 ms.
   const bool whole = r.e0 == 0 && r.e1 == a.numElems && r.tile0 == 0;
-  bool compact = whole && es.fusedCtrl && r.tile1 - r.tile0 >= 1024;
-  if (DGB_KNOB("DGB_ENC_COMPACT", -1) >= 0) compact = whole && es.fusedCtrl && DGB_KNOB("DGB_ENC_COMPACT", -1) != 0; // experiment knob
+  const bool compact = whole && es.fusedCtrl && DGB_KNOB("DGB_ENC_COMPACT", 0) != 0; // experiment knob
   if (compact) {
     p.tileWords = es.fusedCtrl + kFusedCtrlFixed + 3 * (size_t)a.numElems;
     p.coalClaim = es.fusedCtrl + kFusedCtrlCoal;
+    p.totalWarps = 0; // all runs come from the counter
   }
   auto launch = [&](auto kern) -> int {
     static DeviceOnce onceByPb[6]; // the instantiations share one function-pointer type

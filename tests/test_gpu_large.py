@@ -1,7 +1,7 @@
 """`-m gpu` tests at sizes the small parity cases do not reach: the schedules and modes that only large inputs
 select (fused kernel in its few-huge-elements mode: sliced split claims, 9 split CTAs per SM; stand-alone split
 dealing work round robin over the list or inside every element; in-kernel compaction of many tiles and groups, in
-the fused kernel and - from 1024 tiles - in the stand-alone encoder). Every case: both compress schedules
+the fused kernel). Every case: both compress schedules
 byte-identical, the CPU oracle byte for byte where it finishes in seconds, the reference's CUDA build (when built)
 under its defined-byte mask, round trip bit exact."""
 import numpy as np
@@ -45,7 +45,7 @@ def _compress_both(ft, ins, counts, pb=10):
 CASES = [
     # (float type, word counts): one huge element (sliced fused mode / round robin over the list) ...
     (BF16, [20 * 1024 * 1024 + 12345]),
-    # ... one of >= 1024 tiles: in the separate schedule the encoder launch then also compacts (k_encode<PB, true>)
+    # ... one of more than 2048 tiles (more blocks than two rounds of resident warps in the separate schedule)
     (BF16, [66 * 1024 * 1024 + 4321]),
     (F32, [17 * 1024 * 1024 + 3]),
     # ... several long elements (round robin inside every element; fused with few elements) ...
