@@ -15,6 +15,6 @@ inline int envInt(const char* name, int dflt) {
 
 #define DGB_KNOB(name, dflt)                      \
   ([]() -> int {                                  \
-    static const int v = ::dgb::envInt(name, dflt); \
-    return v;                                     \
+    static const int dgbKnobValue_ = ::dgb::envInt(name, dflt); \
+    return dgbKnobValue_;                         \
   }())
