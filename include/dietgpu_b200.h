@@ -160,7 +160,9 @@ int dgb_float_get_compressed_info(const void* const* in, int in_is_device, uint3
  *     copied, its size is still reported and the call returns DGB_ERR_INVALID_ARG;
  *   - decompress: in_bytes[i] = size of archive i as reported by compress;
  *   - the calls are ordered after the work already enqueued on `stream` and return when every result is in
- *     host memory. Device staging is cached per device until dgb_host_release(). */
+ *     host memory. Device staging is cached per device until dgb_host_release();
+ *   - thread safe: concurrent callers on the same device take turns (one pipeline and one lock per device), callers
+ *     on different devices do not wait for each other. */
 int dgb_float_compress_host(int float_type, int prob_bits, int use_checksum, uint32_t num_in_batch,
                             const void* const* in, const uint32_t* in_size, void* const* out,
                             const uint32_t* out_capacity, uint32_t* out_size, void* stream);
